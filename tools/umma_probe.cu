@@ -1,0 +1,454 @@
+// On-GPU probe for the tcgen05 building blocks the NRC kernels rely on. Not product code: it
+// validates descriptor encodings / operand layouts against a host GEMM and measures a few
+// per-SM rates (MMA issue, TMEM load) that size the kernel design. Build: tools/build_probe.sh
+//   umma_probe func <case>      functional case, prints PASS/FAIL and the lane mapping found
+//   umma_probe rate             timing microbenchmarks (cycles)
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <vector>
+#include <string>
+#include <cuda_runtime.h>
+#include "../neural-radiance-caching_b200/csrc/sm100_prims.cuh"
+
+using namespace nrcb;
+
+#define CK(x)                                                                              \
+    do {                                                                                   \
+        cudaError_t e_ = (x);                                                              \
+        if (e_ != cudaSuccess) {                                                           \
+            printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); \
+            exit(2);                                                                       \
+        }                                                                                  \
+    } while (0)
+
+struct ProbeArgs {
+    uint32_t a_bytes, b_bytes;     // smem image sizes (a_bytes unused in tmem mode)
+    uint32_t a_lbo, a_sbo, a_kstep;  // smem A descriptor (bytes); in tmem mode a_kstep = columns per MMA
+    uint32_t b_lbo, b_sbo, b_kstep;
+    uint32_t idesc, nk, a_tmem, a_cols, n_cols;
+};
+
+// smem: [A image | B image], 1024-aligned
+__global__ void __launch_bounds__(128, 1)
+probe_func(const uint8_t* __restrict__ a_img, const uint8_t* __restrict__ b_img, float* __restrict__ d_out,
+           ProbeArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    uint8_t* sa = smem;
+    uint8_t* sb = smem + ((p.a_bytes + 1023) & ~1023u);
+    if (!p.a_tmem)
+        for (uint32_t i = tid * 16; i < p.a_bytes; i += 128 * 16) *(uint4*)(sa + i) = *(const uint4*)(a_img + i);
+    for (uint32_t i = tid * 16; i < p.b_bytes; i += 128 * 16) *(uint4*)(sb + i) = *(const uint4*)(b_img + i);
+    if (tid == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base_s;
+    const uint32_t lane_addr = tb + ((warp * 32u) << 16);
+    // sentinel-fill D columns [0, n_cols) so untouched lanes are recognisable
+    {
+        uint32_t s[16];
+        for (int i = 0; i < 16; ++i) s[i] = __float_as_uint(12345.0f);
+        for (uint32_t c = 0; c < p.n_cols; c += 16) tmem_st16(lane_addr + c, s);
+        tmem_wait_st();
+    }
+    if (p.a_tmem) {  // A image = uint32[128][a_cols], packed half2 (lo = even k)
+        const uint32_t* arow = (const uint32_t*)a_img + (size_t)tid * p.a_cols;
+        for (uint32_t c = 0; c < p.a_cols; c += 8) {
+            uint32_t v[8];
+            for (int i = 0; i < 8; ++i) v[i] = arow[c + i];
+            tmem_st8(lane_addr + 256 + c, v);
+        }
+        tmem_wait_st();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+        tc_fence_after();
+        for (uint32_t k = 0; k < p.nk; ++k) {
+            uint64_t bd = umma_desc(smem_u32(sb) + k * p.b_kstep, p.b_lbo, p.b_sbo);
+            if (p.a_tmem) {
+                umma_ts(tb, tb + 256 + k * p.a_kstep, bd, p.idesc, k > 0);
+            } else {
+                uint64_t ad = umma_desc(smem_u32(sa) + k * p.a_kstep, p.a_lbo, p.a_sbo);
+                umma_ss(tb, ad, bd, p.idesc, k > 0);
+            }
+        }
+        umma_commit(&bar);
+    }
+    mbar_wait(&bar, 0);
+    tc_fence_after();
+    for (uint32_t c = 0; c < p.n_cols; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(lane_addr + c, v);
+        tmem_wait_ld();
+        for (int i = 0; i < 16; ++i) d_out[(size_t)tid * p.n_cols + c + i] = __uint_as_float(v[i]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+// ------------------------------------------------------------------ host side
+static uint16_t f2h(float f) { __half h = __float2half_rn(f); uint16_t u; memcpy(&u, &h, 2); return u; }
+static float h2f(uint16_t u) { __half h; memcpy(&h, &u, 2); return __half2float(h); }
+
+// X[rows][k] -> K-major interleaved image: off = (k/8)*lbo + (r/8)*128 + (r%8)*16 + (k%8)*2, lbo = rows/8*128
+static std::vector<uint8_t> img_kmajor(const std::vector<float>& X, int rows, int K) {
+    std::vector<uint8_t> img((size_t)rows * K * 2, 0);
+    uint32_t lbo = rows / 8 * 128;
+    for (int r = 0; r < rows; ++r)
+        for (int k = 0; k < K; ++k) {
+            uint32_t off = (k / 8) * lbo + (r / 8) * 128 + (r % 8) * 16 + (k % 8) * 2;
+            uint16_t h = f2h(X[(size_t)r * K + k]);
+            memcpy(&img[off], &h, 2);
+        }
+    return img;
+}
+
+static std::vector<float> rand_mat(int r, int c, uint32_t seed) {
+    std::vector<float> m((size_t)r * c);
+    uint32_t s = seed * 2654435761u + 12345u;
+    for (auto& v : m) {
+        s = s * 1664525u + 1013904223u;
+        v = h2f(f2h(((int)((s >> 9) & 1023) - 512) / 256.0f));
+    }
+    return m;
+}
+
+// Compare dump[128][ncols] with expected E[M][N] under lane mapping `map(row)->lane`
+static double cmp_map(const std::vector<float>& dump, int ncols, const std::vector<float>& E, int M, int N, int kind) {
+    double maxerr = 0;
+    for (int r = 0; r < M; ++r) {
+        int lane = kind == 0 ? r : (r / 16) * 32 + (r % 16);
+        if (lane >= 128) return 1e30;
+        for (int n = 0; n < N; ++n) {
+            double e = fabs((double)dump[(size_t)lane * ncols + n] - (double)E[(size_t)r * N + n]);
+            if (!(e <= maxerr)) maxerr = e;
+        }
+    }
+    return maxerr;
+}
+
+static int run_func(const std::string& name) {
+    int M = 128, N = 64, K = 64;
+    bool a_tmem = false, mn = false;
+    if (name == "ss_k") {}
+    else if (name == "ss_k80") { K = 80; }
+    else if (name == "ss_n16") { N = 16; }
+    else if (name == "ts") { a_tmem = true; }
+    else if (name == "ts_k80") { a_tmem = true; K = 80; }
+    else if (name == "ts_n16") { a_tmem = true; N = 16; }
+    else if (name == "mn_m64") { M = 64; N = 64; K = 128; mn = true; }
+    else if (name == "mn_m64_n80") { M = 64; N = 80; K = 128; mn = true; }
+    else if (name == "mn_m128") { M = 128; N = 64; K = 128; mn = true; }
+    else { printf("unknown case %s\n", name.c_str()); return 2; }
+
+    std::vector<float> A = rand_mat(M, K, 1), B = rand_mat(N, K, 2), E((size_t)M * N);
+    for (int m = 0; m < M; ++m)
+        for (int n = 0; n < N; ++n) {
+            double acc = 0;
+            for (int k = 0; k < K; ++k) acc += (double)A[(size_t)m * K + k] * B[(size_t)n * K + k];
+            E[(size_t)m * N + n] = (float)acc;
+        }
+    ProbeArgs p{};
+    std::vector<uint8_t> aimg, bimg;
+    p.nk = K / 16;
+    p.n_cols = (N + 15) / 16 * 16;
+    if (!mn) {
+        bimg = img_kmajor(B, N, K);
+        p.b_lbo = N / 8 * 128; p.b_sbo = 128; p.b_kstep = 2 * p.b_lbo;
+        if (a_tmem) {
+            p.a_tmem = 1; p.a_cols = K / 2; p.a_kstep = 8;
+            aimg.resize((size_t)128 * p.a_cols * 4);
+            for (int m = 0; m < 128; ++m)
+                for (int k = 0; k < K; k += 2) {
+                    uint32_t w = (uint32_t)f2h(A[(size_t)m * K + k]) | ((uint32_t)f2h(A[(size_t)m * K + k + 1]) << 16);
+                    memcpy(&aimg[((size_t)m * p.a_cols + k / 2) * 4], &w, 4);
+                }
+        } else {
+            aimg = img_kmajor(A, M, K);
+            p.a_lbo = M / 8 * 128; p.a_sbo = 128; p.a_kstep = 2 * p.a_lbo;
+        }
+        p.idesc = umma_idesc_f16(M, N, 0, 0);
+    } else {
+        // operands are stored sample-major: Xs[k=sample][m=feat] in the K-major interleaved image of a
+        // [K samples x M feats] matrix; the MMA consumes them as MN-major A[m][k] / B[n][k].
+        std::vector<float> As((size_t)K * M), Bs((size_t)K * N);
+        for (int m = 0; m < M; ++m) for (int k = 0; k < K; ++k) As[(size_t)k * M + m] = A[(size_t)m * K + k];
+        for (int n = 0; n < N; ++n) for (int k = 0; k < K; ++k) Bs[(size_t)k * N + n] = B[(size_t)n * K + k];
+        aimg = img_kmajor(As, K, M);
+        bimg = img_kmajor(Bs, K, N);
+        p.a_sbo = K / 8 * 128; p.a_lbo = 128; p.a_kstep = 256;
+        p.b_sbo = K / 8 * 128; p.b_lbo = 128; p.b_kstep = 256;
+        p.idesc = umma_idesc_f16(M, N, 1, 1);
+    }
+    p.a_bytes = a_tmem ? 0 : (uint32_t)aimg.size();
+    p.b_bytes = (uint32_t)bimg.size();
+    uint8_t *da, *db; float* dd;
+    CK(cudaMalloc(&da, aimg.size())); CK(cudaMalloc(&db, bimg.size()));
+    CK(cudaMalloc(&dd, (size_t)128 * p.n_cols * 4));
+    CK(cudaMemcpy(da, aimg.data(), aimg.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(db, bimg.data(), bimg.size(), cudaMemcpyHostToDevice));
+    size_t smem = ((p.a_bytes + 1023) & ~1023u) + p.b_bytes + 1024;
+    CK(cudaFuncSetAttribute(probe_func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    probe_func<<<1, 128, smem>>>(da, db, dd, p);
+    CK(cudaDeviceSynchronize());
+    std::vector<float> dump((size_t)128 * p.n_cols);
+    CK(cudaMemcpy(dump.data(), dd, dump.size() * 4, cudaMemcpyDeviceToHost));
+    double e0 = cmp_map(dump, p.n_cols, E, M, N, 0), e1 = cmp_map(dump, p.n_cols, E, M, N, 1);
+    int untouched = 0;
+    for (int l = 0; l < 128; ++l) if (dump[(size_t)l * p.n_cols] == 12345.0f) untouched++;
+    printf("case %-12s M=%d N=%d K=%d idesc=%08x  err(lane=row)=%.4g err(lane=16in32)=%.4g untouched_lanes=%d  %s\n",
+           name.c_str(), M, N, K, p.idesc, e0, e1, untouched, (e0 < 1e-2 || e1 < 1e-2) ? "PASS" : "FAIL");
+    if (!(e0 < 1e-2 || e1 < 1e-2)) {
+        printf("  first row dump: ");
+        for (int n = 0; n < 8; ++n) printf("%g ", dump[n]);
+        printf("\n  expected      : ");
+        for (int n = 0; n < 8; ++n) printf("%g ", E[n]);
+        printf("\n");
+    }
+    return (e0 < 1e-2 || e1 < 1e-2) ? 0 : 1;
+}
+
+// ------------------------------------------------------------------ rate probes
+// Clean issue-rate probe: compile-time N / accumulator count, no per-iteration register->uniform moves.
+// ELECT=1 issues from a converged warp through elect.sync (CUTLASS style), 0 from `if (tid == 0)`.
+template <int N, int NACC, bool TS, bool ELECT>
+__global__ void __launch_bounds__(128, 1) probe_issue(int reps, long long* out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    for (uint32_t i = tid * 16; i < 48 * 1024; i += blockDim.x * 16) *(uint4*)(smem + i) = make_uint4(0, 0, 0, 0);
+    if (tid == 0) { mbar_init(&bar, 1); fence_mbar_init(); }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base_s;
+    constexpr int DSTRIDE = N < 32 ? 32 : N;
+    if (warp == 0) {
+        bool leader;
+        if (ELECT) {
+            uint32_t pred;
+            asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+            leader = pred != 0;
+        } else leader = (tid == 0);
+        long long t0 = 0, t1 = 0;
+        if (leader) {
+            const uint32_t idesc = umma_idesc_f16(128, N, 0, 0);
+            const uint64_t ad = umma_desc(smem_u32(smem), 2048, 128);
+            const uint64_t bd = umma_desc(smem_u32(smem) + 16384, N / 8 * 128, 128);
+            t0 = clock64();
+            for (int i = 0; i < reps; i += 4) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t d = tb + (uint32_t)((j % NACC) * DSTRIDE);
+                    if (TS) umma_ts(d, tb + 480, bd, idesc, 1); else umma_ss(d, ad, bd, idesc, 1);
+                }
+            }
+            t1 = clock64();
+            umma_commit(&bar);
+        }
+        __syncwarp();
+        mbar_wait(&bar, 0);
+        long long t2 = clock64();
+        if (leader) { out[0] = t1 - t0; out[1] = t2 - t0; }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tb, 512);
+}
+template <int N, int NACC, bool TS, bool ELECT>
+static void run_issue(long long* dout) {
+    long long h[4];
+    auto k = probe_issue<N, NACC, TS, ELECT>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    for (int rep = 0; rep < 2; ++rep) {
+        k<<<1, 128, 64 * 1024>>>(512, dout);
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(h, dout, 32, cudaMemcpyDeviceToHost));
+    }
+    printf("issue %s N=%3d nacc=%d elect=%d x512: issue %6lld total %6lld  per-MMA %.1f\n", TS ? "TS" : "SS", N, NACC, (int)ELECT,
+           h[0], h[1], h[1] / 512.0);
+}
+
+// mode 0: SS MMA M128 N64, 1: TS MMA M128 N64, 2: SS N16, 3: TS N16  -> cycles for `reps` MMAs (one batch)
+// mode 4: batch-of-4 MMA latency (issue..commit observed), averaged over reps
+// mode 5: TMEM ld32 throughput with blockDim/32 warps, reps loads each
+// mode 6: epilogue emulation: ld 64 cols + relu/pack + st 32 cols per iteration
+// mode 7: STS.128 of a 128x64 fp16 tile (interleaved layout) per iteration
+__global__ void __launch_bounds__(512, 1) probe_rate(int mode, int reps, long long* out) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ long long tmin, tmax;
+    const uint32_t tid = threadIdx.x, warp = tid >> 5;
+    for (uint32_t i = tid * 16; i < 48 * 1024; i += blockDim.x * 16) *(uint4*)(smem + i) = make_uint4(0, 0, 0, 0);
+    if (tid == 0) { mbar_init(&bar, 1); fence_mbar_init(); tmin = (1ll << 62); tmax = 0; }
+    if (warp == 0) tmem_alloc(&tmem_base_s, 512);
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tb = tmem_base_s;
+    const uint32_t lane_addr = tb + (((warp & 3) * 32u) << 16);
+    if (mode == 8 || mode == 9) {
+        // mode 8: SS, mode 9: TS; reps = total MMAs; out[2] = (nacc<<16)|N on entry
+        if (tid == 0) {
+            const int nacc = (int)(out[2] >> 16), N = (int)(out[2] & 0xffff);
+            const uint32_t idesc = umma_idesc_f16(128, N, 0, 0);
+            const uint64_t ad = umma_desc(smem_u32(smem), 2048, 128);
+            const uint64_t bd = umma_desc(smem_u32(smem) + 16384, N / 8 * 128, 128);
+            long long t0 = clock64();
+            for (int i = 0; i < reps; ++i) {
+                const uint32_t d = tb + (uint32_t)(i % nacc) * (uint32_t)(N < 32 ? 32 : N);
+                if (mode == 9) umma_ts(d, tb + 480, bd, idesc, 1); else umma_ss(d, ad, bd, idesc, 1);
+            }
+            long long t1 = clock64();
+            umma_commit(&bar);
+            mbar_wait(&bar, 0);
+            long long t2 = clock64();
+            out[0] = t1 - t0; out[1] = t2 - t0;
+        }
+    } else if (mode <= 4) {
+        if (tid == 0) {
+            const int N = (mode == 2 || mode == 3) ? 16 : 64;
+            const bool ts = (mode == 1 || mode == 3);
+            const uint32_t idesc = umma_idesc_f16(128, N, 0, 0);
+            const uint64_t ad = umma_desc(smem_u32(smem), 2048, 128);
+            const uint64_t bd = umma_desc(smem_u32(smem) + 16384, N / 8 * 128, 128);
+            uint32_t parity = 0;
+            if (mode < 4) {
+                long long t0 = clock64();
+                for (int i = 0; i < reps; ++i) {
+                    if (ts) umma_ts(tb, tb + 256, bd, idesc, 1); else umma_ss(tb, ad, bd, idesc, 1);
+                }
+                long long t1 = clock64();
+                umma_commit(&bar);
+                mbar_wait(&bar, parity);
+                long long t2 = clock64();
+                out[0] = t1 - t0; out[1] = t2 - t0;
+            } else {
+                long long t0 = clock64();
+                for (int i = 0; i < reps; ++i) {
+                    for (int k = 0; k < 4; ++k) umma_ss(tb, ad, bd, idesc, k > 0);
+                    umma_commit(&bar);
+                    mbar_wait(&bar, parity);
+                    parity ^= 1;
+                }
+                out[0] = (clock64() - t0) / reps; out[1] = 0;
+            }
+        }
+    } else {
+        __syncthreads();
+        long long t0 = clock64();
+        uint32_t acc = 0;
+        if (mode == 5) {
+            for (int i = 0; i < reps; ++i) {
+                uint32_t v[32];
+                tmem_ld32(lane_addr + (i & 1) * 32, v);
+                tmem_wait_ld();
+                acc += v[0] + v[31];
+            }
+        } else if (mode == 6) {
+            for (int i = 0; i < reps; ++i) {
+                uint32_t v[32], w[16];
+                tmem_ld32(lane_addr, v);
+                tmem_wait_ld();
+                for (int j = 0; j < 16; ++j) w[j] = pack_relu_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                tmem_st16(lane_addr + 256, w);
+                tmem_ld32(lane_addr + 32, v);
+                tmem_wait_ld();
+                for (int j = 0; j < 16; ++j) w[j] = pack_relu_h2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                tmem_st16(lane_addr + 256 + 16, w);
+                tmem_wait_st();
+                acc += w[3];
+            }
+        } else {
+            const uint32_t row = tid & 127;
+            for (int i = 0; i < reps; ++i) {
+                for (int c = 0; c < 8; ++c)
+                    *(uint4*)(smem + c * 2048 + (row / 8) * 128 + (row % 8) * 16) = make_uint4(i, c, row, acc);
+                acc += i;
+            }
+        }
+        long long t1 = clock64();
+        atomicMin(&tmin, t0);
+        atomicMax(&tmax, t1);
+        if (acc == 0xdeadbeef) out[3] = acc;
+        __syncthreads();
+        if (tid == 0) { out[0] = tmax - tmin; out[1] = t1 - t0; }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+static void run_rate() {
+    long long* dout; CK(cudaMalloc(&dout, 64));
+    CK(cudaFuncSetAttribute(probe_rate, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    struct { int mode, reps, threads; const char* what; } cases[] = {
+        {0, 256, 128, "SS M128 N64 K16 x256 (issue cyc, total cyc)"},
+        {1, 256, 128, "TS M128 N64 K16 x256"},
+        {2, 256, 128, "SS M128 N16 K16 x256"},
+        {3, 256, 128, "TS M128 N16 K16 x256"},
+        {0, 1024, 128, "SS M128 N64 K16 x1024"},
+        {1, 1024, 128, "TS M128 N64 K16 x1024"},
+        {4, 64, 128, "batch of 4 MMAs issue->commit->wait (avg cyc)"},
+        {5, 256, 128, "tmem ld32 x256, 4 warps"},
+        {5, 256, 256, "tmem ld32 x256, 8 warps"},
+        {5, 256, 512, "tmem ld32 x256, 16 warps"},
+        {6, 128, 128, "epilogue emu (ld64+cvt+st32) x128, 4 warps"},
+        {6, 128, 256, "epilogue emu x128, 8 warps"},
+        {6, 128, 512, "epilogue emu x128, 16 warps"},
+        {7, 128, 128, "STS 128x64 fp16 tile x128, 4 warps"},
+        {7, 128, 512, "STS 128x64 fp16 tile x128, 16 warps"},
+    };
+    run_issue<64, 1, false, false>(dout); run_issue<64, 1, false, true>(dout);
+    run_issue<64, 2, false, true>(dout);  run_issue<64, 4, false, true>(dout);
+    run_issue<64, 1, true, true>(dout);   run_issue<64, 4, true, true>(dout);
+    run_issue<16, 1, false, true>(dout);  run_issue<16, 4, false, true>(dout);
+    run_issue<128, 1, false, true>(dout); run_issue<128, 2, false, true>(dout);
+    run_issue<256, 1, false, true>(dout); run_issue<256, 1, true, true>(dout);
+    for (int mode = 8; mode <= 9; ++mode)
+        for (int N : {16, 64, 128, 256})
+            for (int nacc : {1, 2, 4}) {
+                if (nacc * (N < 32 ? 32 : N) > 448) continue;
+                long long h[4];
+                for (int rep = 0; rep < 2; ++rep) {
+                    long long init[4] = {0, 0, ((long long)nacc << 16) | N, 0};
+                    CK(cudaMemcpy(dout, init, 32, cudaMemcpyHostToDevice));
+                    probe_rate<<<1, 128, 64 * 1024>>>(mode, 512, dout);
+                    CK(cudaDeviceSynchronize());
+                    CK(cudaMemcpy(h, dout, 32, cudaMemcpyDeviceToHost));
+                }
+                printf("rate %s N=%3d nacc=%d x512: issue %6lld total %6lld  per-MMA %.1f\n", mode == 8 ? "SS" : "TS", N, nacc,
+                       h[0], h[1], h[1] / 512.0);
+            }
+    for (auto& c : cases) {
+        for (int rep = 0; rep < 2; ++rep) {
+            CK(cudaMemset(dout, 0, 64));
+            probe_rate<<<1, c.threads, 64 * 1024>>>(c.mode, c.reps, dout);
+            CK(cudaDeviceSynchronize());
+        }
+        long long h[4]; CK(cudaMemcpy(h, dout, 32, cudaMemcpyDeviceToHost));
+        printf("rate mode %d reps %4d thr %3d: %8lld %8lld  per-rep %.1f  | %s\n", c.mode, c.reps, c.threads, h[0], h[1],
+               (double)(c.mode < 4 ? h[1] : h[0]) / (c.mode == 4 ? 1 : c.reps), c.what);
+    }
+}
+
+int main(int argc, char** argv) {
+    if (argc >= 3 && !strcmp(argv[1], "func")) return run_func(argv[2]);
+    if (argc >= 2 && !strcmp(argv[1], "rate")) { run_rate(); return 0; }
+    printf("usage: umma_probe func <case> | rate\n");
+    return 2;
+}
