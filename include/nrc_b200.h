@@ -1,0 +1,101 @@
+/* nrc_b200.h -- C ABI of the B200-native neural radiance cache.
+ *
+ * Drop-in boundary for the reference's cache interface `class nrc::Network`
+ * (/root/reference/nrc/inc/NRCNetwork.h:20-75, implemented in nrc/src/NRCNetwork.cu:22-128).
+ * Plain pointers and sizes only; every function returns 0 on success or a negative nrc_b200_status and
+ * leaves a message for nrc_b200_last_error().  The C++ shim include/NRCNetwork_b200.h re-creates
+ * `nrc::Network` on top of these calls with the reference's exact signatures and exception behaviour.
+ *
+ * Data contract (unchanged from the reference, nrc/src/NRCNetwork.cu:41-83, nrc/src/Device.cpp:198,1272-1288):
+ *   queries   : device pointer, `n` records of 15 float32 (nrc::RadianceQuery, 60 B, sample-major)
+ *   radiance  : device pointer, `n` records of 3 float32
+ *   train     : exactly NRC_B200_BATCH_SIZE (16384) queries + targets per call
+ * Unlike the reference, rows in [n, round_up(n,256)) of the caller's buffers are never touched.
+ */
+#ifndef NRC_B200_H
+#define NRC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NRC_B200_INPUT_DIMS 15       /* nrc::NN_INPUT_DIMS,  neural_radiance_caching.h:35-43 */
+#define NRC_B200_OUTPUT_DIMS 3       /* nrc::NN_OUTPUT_DIMS, neural_radiance_caching.h:44    */
+#define NRC_B200_BATCH_SIZE 16384    /* nrc::BATCH_SIZE,     neural_radiance_caching.h:31    */
+#define NRC_B200_NUM_BATCHES 4       /* nrc::NUM_BATCHES,    neural_radiance_caching.h:29    */
+
+typedef enum nrc_b200_encoding {     /* nrc::InputEncoding, neural_radiance_caching.h:24-27 */
+    NRC_B200_FREQUENCY = 0,
+    NRC_B200_HASH = 1
+} nrc_b200_encoding;
+
+typedef enum nrc_b200_status {
+    NRC_B200_OK = 0,
+    NRC_B200_ERR_INVALID = -1,   /* bad argument (reference: std::invalid_argument, NRCNetworkConfigs.h:129-131) */
+    NRC_B200_ERR_CUDA = -2,      /* CUDA runtime failure (reference: std::runtime_error from CUDA_CHECK_THROW) */
+    NRC_B200_ERR_DESTROYED = -3  /* informational: call on a destroyed handle is a no-op (NRCNetwork.cu:43,66) */
+} nrc_b200_status;
+
+typedef struct nrc_b200_network* nrc_b200_handle;
+
+/* Network::init<>(stream, encoding)  NRCNetwork.h:26-31, NRCNetwork.cu:106-112.
+ * Creates model + optimizer state on the current CUDA device; `cu_stream` is a CUstream / cudaStream_t.
+ * `log2_hashmap_size` <= 0 selects the reference's 15 (NRCNetworkConfigs.h:101); `seed` seeds the
+ * xavier-uniform initialisation (the reference uses 1337, trainer.h:50-57). */
+int nrc_b200_create(int encoding, void* cu_stream, nrc_b200_handle* out);
+int nrc_b200_create_ex(int encoding, int log2_hashmap_size, uint64_t seed, void* cu_stream, nrc_b200_handle* out);
+/* Network::destroy()  NRCNetwork.cu:35-39 */
+int nrc_b200_destroy(nrc_b200_handle h);
+/* Network::init on a live object = full reset (new weights, optimizer state zeroed)  Device.cpp:2415-2421 */
+int nrc_b200_reset(nrc_b200_handle h, int encoding);
+
+/* Network::infer(inputs_d, outputs_d, numInputs[, stream])  NRCNetwork.cu:64-83.  Asynchronous.
+ * Uses the EMA weights (trainer.h:329-335).  `cu_stream` NULL = the stream last set. */
+int nrc_b200_infer(nrc_b200_handle h, const float* queries_d, float* radiance_d, uint32_t n, void* cu_stream);
+/* Network::train(batchInputs_d, batchTargets_d[, stream], loss_h)  NRCNetwork.cu:41-62.
+ * One optimizer step on 16384 samples.  loss_h == NULL: asynchronous.  loss_h != NULL: the loss of this
+ * step is written to *loss_h after a stream synchronisation, as in the reference (reduce_sum.h:146-149). */
+int nrc_b200_train(nrc_b200_handle h, const float* queries_d, const float* targets_d, void* cu_stream, float* loss_h);
+
+/* Network::setStream  NRCNetwork.cu:85-88 */
+int nrc_b200_set_stream(nrc_b200_handle h, void* cu_stream);
+/* Network::setHyperParams / getLearningRate  NRCNetwork.cu:90-104 */
+int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr);
+int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr);
+
+/* ---- additions without a reference counterpart ------------------------------------------------------ */
+/* Host-buffer query: pinned staging + chunked H2D / kernel / D2H pipeline inside the call (synchronous). */
+int nrc_b200_infer_host(nrc_b200_handle h, const float* queries_h, float* radiance_h, uint32_t n);
+/* Device-side loss of the most recent train() call, without forcing a sync on the training stream. */
+int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d);
+
+/* Data-parallel training: a rank computes the fp32 gradient of its shard of a global batch
+ * (normalised by 3*global_n) into a device buffer the caller all-reduces (NCCL sum), then every rank applies
+ * the identical Adam+EMA step.  grad_d has nrc_b200_n_params() floats. */
+int nrc_b200_train_grad(nrc_b200_handle h, const float* queries_d, const float* targets_d, uint32_t n_local,
+                        uint32_t n_global, float** grad_d, void* cu_stream);
+int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h);
+
+/* Parity-harness access to the parameters (Trainer::params() / set_params(), trainer.h:226-269). */
+typedef enum nrc_b200_param_kind {
+    NRC_B200_PARAMS_MASTER_F32 = 0,  /* fp32 master weights  */
+    NRC_B200_PARAMS_TRAIN_F16 = 1,   /* fp16 training weights */
+    NRC_B200_PARAMS_EMA_F16 = 2,     /* fp16 EMA = inference weights */
+    NRC_B200_PARAMS_GRAD_F16 = 3,    /* fp16 gradient of the last step (loss-scaled by 128) */
+    NRC_B200_ADAM_M1_F32 = 4,
+    NRC_B200_ADAM_M2_F32 = 5
+} nrc_b200_param_kind;
+int nrc_b200_n_params(nrc_b200_handle h, uint32_t* n_params, uint32_t* n_mlp_params);
+int nrc_b200_get_params(nrc_b200_handle h, int kind, void* dst_host);   /* synchronises the stream */
+int nrc_b200_set_params(nrc_b200_handle h, int kind, const void* src_host);
+/* Loads fp32 master weights, derives the fp16 training copy, zeroes EMA/Adam state and the step counter. */
+int nrc_b200_load_master(nrc_b200_handle h, const float* master_host);
+
+const char* nrc_b200_last_error(void);
+/* Number of kernel launches issued through this handle so far (bench.py's gpu_launches). */
+int nrc_b200_launch_count(nrc_b200_handle h, uint64_t* count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,210 @@
+"""nrc_b200 -- Python binding of the B200-native neural radiance cache (C ABI in include/nrc_b200.h).
+
+The directory name carries a hyphen (it mirrors the reference repo's name), so import it through
+``__graft_entry__.load_package()`` which registers it as ``nrc_b200``.
+
+``Network`` mirrors the reference's cache interface ``nrc::Network``
+(/root/reference/nrc/inc/NRCNetwork.h:20-75): same method names, argument meaning and error behaviour
+(exceptions instead of status codes, silent no-ops after ``destroy``).  Device buffers are raw device
+pointers (ints) or torch CUDA tensors; torch is only used for memory and streams.
+
+There is NO CPU path: if libnrc_b200.so is missing, or the device is not sm_100, construction raises.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnrc_b200.so")
+
+FREQUENCY, HASH = 0, 1            # nrc::InputEncoding (neural_radiance_caching.h:24-27)
+NUM_BATCHES = 4                   # neural_radiance_caching.h:29
+BATCH_SIZE = 16384                # neural_radiance_caching.h:31
+NN_INPUT_DIMS, NN_OUTPUT_DIMS = 15, 3
+
+PARAMS_MASTER_F32, PARAMS_TRAIN_F16, PARAMS_EMA_F16, PARAMS_GRAD_F16, ADAM_M1_F32, ADAM_M2_F32 = range(6)
+
+# every symbol include/nrc_b200.h declares (tests check the library exports all of them)
+ABI_SYMBOLS = [
+    "nrc_b200_create", "nrc_b200_create_ex", "nrc_b200_destroy", "nrc_b200_reset", "nrc_b200_infer",
+    "nrc_b200_train", "nrc_b200_set_stream", "nrc_b200_set_learning_rate", "nrc_b200_get_learning_rate",
+    "nrc_b200_infer_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
+    "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
+    "nrc_b200_last_error", "nrc_b200_launch_count",
+]
+
+
+def build(verbose=False):
+    """Compile csrc/*.cu for sm_100a into libnrc_b200.so (nvcc cross-compiles without a GPU)."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc")], capture_output=True, text=True)
+    if verbose or r.returncode != 0:
+        print(r.stdout[-4000:], r.stderr[-4000:])
+    if r.returncode != 0:
+        raise RuntimeError("building libnrc_b200.so failed")
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    """The loaded C-ABI library.  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing: run __graft_entry__.build() (there is no fallback path)")
+        L = ctypes.CDLL(LIB_PATH)
+        vp, u32, u64, f32, i32 = ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float, ctypes.c_int
+        P = ctypes.POINTER
+        L.nrc_b200_create.argtypes = [i32, vp, P(vp)]
+        L.nrc_b200_create_ex.argtypes = [i32, i32, u64, vp, P(vp)]
+        L.nrc_b200_destroy.argtypes = [vp]
+        L.nrc_b200_reset.argtypes = [vp, i32]
+        L.nrc_b200_infer.argtypes = [vp, vp, vp, u32, vp]
+        L.nrc_b200_train.argtypes = [vp, vp, vp, vp, P(f32)]
+        L.nrc_b200_set_stream.argtypes = [vp, vp]
+        L.nrc_b200_set_learning_rate.argtypes = [vp, f32]
+        L.nrc_b200_get_learning_rate.argtypes = [vp, P(f32)]
+        L.nrc_b200_infer_host.argtypes = [vp, vp, vp, u32]
+        L.nrc_b200_last_loss_device.argtypes = [vp, P(vp)]
+        L.nrc_b200_train_grad.argtypes = [vp, vp, vp, u32, u32, P(vp), vp]
+        L.nrc_b200_train_apply.argtypes = [vp, vp, P(f32)]
+        L.nrc_b200_n_params.argtypes = [vp, P(u32), P(u32)]
+        L.nrc_b200_get_params.argtypes = [vp, i32, vp]
+        L.nrc_b200_set_params.argtypes = [vp, i32, vp]
+        L.nrc_b200_load_master.argtypes = [vp, vp]
+        L.nrc_b200_last_error.restype = ctypes.c_char_p
+        L.nrc_b200_launch_count.argtypes = [vp, P(u64)]
+        _lib = L
+    return _lib
+
+
+def _ptr(x):
+    """Raw device/host pointer of a torch tensor, numpy array, ctypes pointer or int."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    if hasattr(x, "ctypes"):
+        return x.ctypes.data
+    return ctypes.cast(x, ctypes.c_void_p).value
+
+
+def _check(rc):
+    if rc == 0 or rc == -3:      # -3: call on a destroyed network, silent no-op (NRCNetwork.cu:43,66)
+        return
+    msg = lib().nrc_b200_last_error().decode()
+    if rc == -1:
+        raise ValueError(msg)    # std::invalid_argument (NRCNetworkConfigs.h:129-131)
+    raise RuntimeError(msg)      # std::runtime_error (CUDA_CHECK_THROW)
+
+
+class HyperParams:               # nrc::HyperParams, NRCNetwork.h:10-13
+    def __init__(self, learningRate):
+        self.learningRate = learningRate
+
+
+class Network:
+    """Mirror of ``nrc::Network``.  ``init`` must be called before use, ``destroy`` explicitly at the end."""
+
+    def __init__(self):
+        self._h = None
+        self._stream = None
+
+    # template<bool Verbose> void init(CUstream, nrc::InputEncoding)     NRCNetwork.h:26-31
+    def init(self, stream, encoding, verbose=False, log2_hashmap_size=15, seed=1337):
+        if self._h is not None:              # init on a live object = full re-create (NRCNetwork.cu:106-112)
+            _check(lib().nrc_b200_destroy(self._h))
+            self._h = None
+        h = ctypes.c_void_p()
+        _check(lib().nrc_b200_create_ex(int(encoding), int(log2_hashmap_size), int(seed), _ptr(stream), ctypes.byref(h)))
+        self._h, self._stream = h, stream
+        if verbose:
+            print(f"nrc_b200 network: encoding={'Frequency' if encoding == 0 else 'Hash'} n_params={self.n_params()}")
+
+    def destroy(self):                       # NRCNetwork.cu:35-39
+        if self._h is not None:
+            _check(lib().nrc_b200_destroy(self._h))
+            self._h = None
+
+    def train(self, batchInputs_d, batchTargets_d, stream=None, want_loss=False):   # NRCNetwork.cu:41-62
+        """One optimizer step on BATCH_SIZE samples.  Returns the loss (host float, forces a stream sync as the
+        reference's loss_h != nullptr path does) when want_loss, else None (asynchronous)."""
+        if self._h is None:
+            return None
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train(self._h, _ptr(batchInputs_d), _ptr(batchTargets_d), _ptr(stream),
+                                    ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
+
+    def infer(self, inputs_d, outputs_d, numInputs, stream=None):                   # NRCNetwork.cu:64-83
+        if self._h is None:
+            return
+        _check(lib().nrc_b200_infer(self._h, _ptr(inputs_d), _ptr(outputs_d), int(numInputs), _ptr(stream)))
+
+    def setStream(self, stream):             # NRCNetwork.cu:85-88
+        if self._h is not None:
+            _check(lib().nrc_b200_set_stream(self._h, _ptr(stream)))
+
+    def setHyperParams(self, hp):            # NRCNetwork.cu:90-94
+        _check(lib().nrc_b200_set_learning_rate(self._h, float(hp.learningRate)))
+
+    def getLearningRate(self):               # NRCNetwork.cu:101-104
+        v = ctypes.c_float()
+        _check(lib().nrc_b200_get_learning_rate(self._h, ctypes.byref(v)))
+        return v.value
+
+    # ---- additions (no reference counterpart) ---------------------------------------------------------
+    def infer_host(self, inputs_h, outputs_h, numInputs):
+        _check(lib().nrc_b200_infer_host(self._h, _ptr(inputs_h), _ptr(outputs_h), int(numInputs)))
+
+    def train_grad(self, inputs_d, targets_d, n_local, n_global, stream=None):
+        """Gradient of this rank's shard; returns the device pointer of the fp32 gradient (n_params floats)."""
+        g = ctypes.c_void_p()
+        _check(lib().nrc_b200_train_grad(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global),
+                                         ctypes.byref(g), _ptr(stream)))
+        return g.value
+
+    def train_apply(self, stream=None, want_loss=False):
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train_apply(self._h, _ptr(stream), ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
+
+    def last_loss_device(self):
+        p = ctypes.c_void_p()
+        _check(lib().nrc_b200_last_loss_device(self._h, ctypes.byref(p)))
+        return p.value
+
+    def n_params(self):
+        a, b = ctypes.c_uint32(), ctypes.c_uint32()
+        _check(lib().nrc_b200_n_params(self._h, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def get_params(self, kind):
+        import numpy as np
+        n, _ = self.n_params()
+        dt = np.float32 if kind in (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32) else np.float16
+        out = np.empty(n, dtype=dt)
+        _check(lib().nrc_b200_get_params(self._h, kind, out.ctypes.data))
+        return out
+
+    def set_params(self, kind, arr):
+        import numpy as np
+        n, _ = self.n_params()
+        dt = np.float32 if kind in (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32) else np.float16
+        a = np.ascontiguousarray(arr, dtype=dt)
+        assert a.size == n
+        _check(lib().nrc_b200_set_params(self._h, kind, a.ctypes.data))
+
+    def load_master(self, master):
+        import numpy as np
+        a = np.ascontiguousarray(master, dtype=np.float32)
+        assert a.size == self.n_params()[0]
+        _check(lib().nrc_b200_load_master(self._h, a.ctypes.data))
+
+    def launch_count(self):
+        c = ctypes.c_uint64()
+        _check(lib().nrc_b200_launch_count(self._h, ctypes.byref(c)))
+        return c.value

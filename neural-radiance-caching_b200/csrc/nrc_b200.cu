@@ -1,0 +1,379 @@
+// Host side of the B200 neural radiance cache: implements the C ABI of include/nrc_b200.h.
+// Mirrors nrc::Network (/root/reference/nrc/src/NRCNetwork.cu) + the parts of tcnn::Trainer it uses
+// (tcnn/include/tiny-cuda-nn/trainer.h:50-95,163-207,322-336): one parameter block
+// [fp32 master | fp16 weights | fp16 EMA | fp16 grads | Adam m, v, steps], everything preallocated at
+// create (no arena, no per-call malloc, no per-step graph capture, no host sync unless loss_h != NULL).
+#include "../../include/nrc_b200.h"
+#include "nrc_kernels.h"
+#include "nrc_encode.cuh"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace nrcb;
+
+static thread_local std::string g_last_error;
+const char* nrc_b200_last_error(void) { return g_last_error.c_str(); }
+
+static int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+#define CU(x)                                                                                     \
+    do {                                                                                          \
+        cudaError_t e_ = (x);                                                                     \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(NRC_B200_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_));      \
+    } while (0)
+
+struct nrc_b200_network {
+    int encoding = 0, log2_hashmap = 15, device = 0, num_sms = 148;
+    uint64_t seed = 1337;
+    cudaStream_t stream = nullptr;
+    uint32_t n_params = 0, n_mlp = 0, enc_width = 80;
+    GridMeta gm{};
+    // parameter block (device)
+    float* master = nullptr; __half* params = nullptr; __half* ema = nullptr; __half* grads = nullptr;
+    float* m1 = nullptr; float* m2 = nullptr; uint32_t* steps = nullptr;
+    // training scratch (device)
+    float* partials = nullptr; float* grid_grad = nullptr; float* loss_partials = nullptr;
+    float* grad_f32 = nullptr; float* loss_d = nullptr;
+    float* loss_pinned = nullptr;
+    // hyper-parameters (NRCNetworkConfigs.h:18-24,43-47,92-97; adam.h defaults)
+    float lr = 1e-3f, beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f, l2_reg = 1e-6f, ema_decay = 0.99f, loss_scale = 128.0f;
+    uint32_t step = 0;
+    uint32_t pending_tiles = 0;  // tiles of the gradient waiting for train_apply
+    // host-buffer inference pipeline
+    static constexpr int kHostChunks = 3;
+    float* pin_in[kHostChunks] = {}; float* pin_out[kHostChunks] = {};
+    float* dev_in[kHostChunks] = {}; float* dev_out[kHostChunks] = {};
+    cudaStream_t hstream[kHostChunks] = {}; cudaEvent_t hevent[kHostChunks] = {};
+    uint32_t host_chunk = 0;
+    uint64_t launches = 0;
+    bool destroyed = false;
+};
+typedef nrc_b200_network Net;
+
+static constexpr uint32_t kMaxTrainTiles = NRC_B200_BATCH_SIZE / 128;
+
+// ---------------------------------------------------------------- model layout
+static void make_layout(Net* n) {
+    n->enc_width = n->encoding == NRC_B200_FREQUENCY ? 80 : 64;
+    n->n_mlp = 64 * n->enc_width + 4 * 64 * 64 + 16 * 64;  // fully_fused_mlp.cu:654-677
+    uint32_t off = 0;
+    memset(&n->gm, 0, sizeof(n->gm));
+    if (n->encoding == NRC_B200_HASH) {
+        for (int l = 0; l < 16; ++l) {  // grid.h:692-723
+            const float scale = exp2f((float)l) * 16.0f - 1.0f;  // common_device.h:856-861
+            const uint32_t res = (uint32_t)ceilf(scale) + 1;
+            const double dense = (double)res * res * res;
+            const uint32_t cap = 1u << n->log2_hashmap;
+            uint32_t size = dense > (double)cap ? cap : (uint32_t)dense;
+            size = (size + 7u) / 8u * 8u;
+            if (size > cap) size = cap;
+            n->gm.offset[l] = off;
+            n->gm.resolution[l] = res;
+            n->gm.scale[l] = scale;
+            if (dense <= (double)size) n->gm.dense_mask |= 1u << l;
+            off += size;
+        }
+        n->gm.offset[16] = off;
+    }
+    n->n_params = n->n_mlp + off * 2;
+}
+
+static uint64_t splitmix64(uint64_t& s) {
+    uint64_t z = (s += 0x9E3779B97F4A7C15ull);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+static float u01(uint64_t& s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16777216.0f); }
+
+static void free_all(Net* n) {
+    cudaFree(n->master); cudaFree(n->params); cudaFree(n->ema); cudaFree(n->grads);
+    cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps);
+    cudaFree(n->partials); cudaFree(n->grid_grad); cudaFree(n->loss_partials); cudaFree(n->grad_f32); cudaFree(n->loss_d);
+    if (n->loss_pinned) cudaFreeHost(n->loss_pinned);
+    n->master = nullptr; n->params = nullptr; n->ema = nullptr; n->grads = nullptr; n->m1 = n->m2 = nullptr;
+    n->steps = nullptr; n->partials = n->grid_grad = n->loss_partials = n->grad_f32 = n->loss_d = nullptr;
+    n->loss_pinned = nullptr;
+    for (int i = 0; i < Net::kHostChunks; ++i) {
+        if (n->pin_in[i]) cudaFreeHost(n->pin_in[i]);
+        if (n->pin_out[i]) cudaFreeHost(n->pin_out[i]);
+        cudaFree(n->dev_in[i]); cudaFree(n->dev_out[i]);
+        if (n->hstream[i]) cudaStreamDestroy(n->hstream[i]);
+        if (n->hevent[i]) cudaEventDestroy(n->hevent[i]);
+        n->pin_in[i] = n->pin_out[i] = n->dev_in[i] = n->dev_out[i] = nullptr;
+        n->hstream[i] = nullptr; n->hevent[i] = nullptr;
+    }
+    n->host_chunk = 0;
+}
+
+// Uploads fp32 master weights, derives the fp16 copy (trainer.h:83-86), zeroes EMA (ema.h:93-94) and Adam state.
+static int upload_master(Net* n, const float* host_master) {
+    std::vector<__half> h(n->n_params);
+    for (uint32_t i = 0; i < n->n_params; ++i) h[i] = __float2half_rn(host_master[i]);
+    CU(cudaMemcpyAsync(n->master, host_master, (size_t)n->n_params * 4, cudaMemcpyHostToDevice, n->stream));
+    CU(cudaMemcpyAsync(n->params, h.data(), (size_t)n->n_params * 2, cudaMemcpyHostToDevice, n->stream));
+    CU(cudaMemsetAsync(n->ema, 0, (size_t)n->n_params * 2, n->stream));
+    CU(cudaMemsetAsync(n->grads, 0, (size_t)n->n_params * 2, n->stream));
+    CU(cudaMemsetAsync(n->m1, 0, (size_t)n->n_params * 4, n->stream));
+    CU(cudaMemsetAsync(n->m2, 0, (size_t)n->n_params * 4, n->stream));
+    CU(cudaMemsetAsync(n->steps, 0, (size_t)n->n_params * 4, n->stream));
+    CU(cudaMemsetAsync(n->grad_f32, 0, (size_t)n->n_params * 4, n->stream));
+    if (n->grid_grad) CU(cudaMemsetAsync(n->grid_grad, 0, (size_t)(n->n_params - n->n_mlp) * 4, n->stream));
+    CU(cudaMemsetAsync(n->loss_d, 0, 4, n->stream));
+    CU(cudaStreamSynchronize(n->stream));  // host vectors go out of scope
+    n->step = 0;
+    n->pending_tiles = 0;
+    return NRC_B200_OK;
+}
+
+// Network::init_ (NRCNetwork.cu:106-112) -> create_from_config -> Trainer ctor -> initialize_params
+// (trainer.h:68-95): xavier-uniform matrices (gpu_matrix.h:284-299, fully_fused_mlp.cu:866-891),
+// grid U(-1e-4, 1e-4) (grid.h:1059-1062).  The random stream is splitmix64(seed), not tcnn's pcg32.
+static int build_model(Net* n) {
+    make_layout(n);
+    n->lr = n->encoding == NRC_B200_FREQUENCY ? 1e-3f : 1e-2f;   // neural_radiance_caching.h:48-55
+    n->eps = n->encoding == NRC_B200_FREQUENCY ? 1e-8f : 1e-15f; // NRCNetworkConfigs.h:96
+    const size_t P = n->n_params;
+    CU(cudaMalloc(&n->master, P * 4)); CU(cudaMalloc(&n->params, P * 2)); CU(cudaMalloc(&n->ema, P * 2));
+    CU(cudaMalloc(&n->grads, P * 2)); CU(cudaMalloc(&n->m1, P * 4)); CU(cudaMalloc(&n->m2, P * 4));
+    CU(cudaMalloc(&n->steps, P * 4)); CU(cudaMalloc(&n->grad_f32, P * 4));
+    CU(cudaMalloc(&n->partials, (size_t)kMaxTrainTiles * n->n_mlp * 4));
+    CU(cudaMalloc(&n->loss_partials, kMaxTrainTiles * 4));
+    CU(cudaMalloc(&n->loss_d, 4));
+    if (P > n->n_mlp) CU(cudaMalloc(&n->grid_grad, (P - n->n_mlp) * 4));
+    CU(cudaMallocHost(&n->loss_pinned, 4));
+    std::vector<float> m(P);
+    uint64_t rng = n->seed;
+    const int E = (int)n->enc_width;
+    const int rows[6] = {64, 64, 64, 64, 64, 16}, cols[6] = {E, 64, 64, 64, 64, 64};
+    size_t o = 0;
+    for (int l = 0; l < 6; ++l) {
+        const float scale = sqrtf(6.0f / (float)(rows[l] + cols[l]));
+        for (int i = 0; i < rows[l] * cols[l]; ++i) m[o++] = u01(rng) * 2 * scale - scale;
+    }
+    for (; o < P; ++o) m[o] = u01(rng) * 2e-4f - 1e-4f;
+    return upload_master(n, m.data());
+}
+
+// ---------------------------------------------------------------- lifecycle
+int nrc_b200_create_ex(int encoding, int log2_hashmap_size, uint64_t seed, void* cu_stream, nrc_b200_handle* out) {
+    if (!out) return fail(NRC_B200_ERR_INVALID, "nrc_b200_create: out is NULL");
+    *out = nullptr;
+    if (encoding != NRC_B200_FREQUENCY && encoding != NRC_B200_HASH)
+        return fail(NRC_B200_ERR_INVALID, "Unsupported input encoding");  // NRCNetworkConfigs.h:129-131
+    if (log2_hashmap_size <= 0) log2_hashmap_size = 15;
+    if (log2_hashmap_size < 12 || log2_hashmap_size > 24)
+        return fail(NRC_B200_ERR_INVALID, "log2_hashmap_size must be in [12, 24]");
+    Net* n = new Net();
+    n->encoding = encoding; n->log2_hashmap = log2_hashmap_size; n->seed = seed; n->stream = (cudaStream_t)cu_stream;
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDevice(&n->device);
+    if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, n->device);
+    if (e != cudaSuccess) { delete n; return fail(NRC_B200_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e)); }
+    if (prop.major != 10) {
+        delete n;
+        return fail(NRC_B200_ERR_CUDA, "nrc_b200 requires an sm_100a (B200) device; found sm_" +
+                                           std::to_string(prop.major * 10 + prop.minor) + ". There is no fallback path.");
+    }
+    n->num_sms = prop.multiProcessorCount;
+    int rc = build_model(n);
+    if (rc != NRC_B200_OK) { free_all(n); delete n; return rc; }
+    *out = n;
+    return NRC_B200_OK;
+}
+int nrc_b200_create(int encoding, void* cu_stream, nrc_b200_handle* out) {
+    return nrc_b200_create_ex(encoding, 15, 1337, cu_stream, out);
+}
+int nrc_b200_destroy(nrc_b200_handle h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (!h->destroyed) { cudaStreamSynchronize(h->stream); free_all(h); h->destroyed = true; }
+    delete h;
+    return NRC_B200_OK;
+}
+int nrc_b200_reset(nrc_b200_handle h, int encoding) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (encoding != NRC_B200_FREQUENCY && encoding != NRC_B200_HASH)
+        return fail(NRC_B200_ERR_INVALID, "Unsupported input encoding");
+    CU(cudaStreamSynchronize(h->stream));
+    free_all(h);
+    h->encoding = encoding;
+    return build_model(h);
+}
+int nrc_b200_set_stream(nrc_b200_handle h, void* s) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    h->stream = (cudaStream_t)s;
+    return NRC_B200_OK;
+}
+int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    h->lr = lr;
+    return NRC_B200_OK;
+}
+int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr) {
+    if (!h || !lr) return fail(NRC_B200_ERR_INVALID, "null argument");
+    *lr = h->lr;
+    return NRC_B200_OK;
+}
+int nrc_b200_launch_count(nrc_b200_handle h, uint64_t* c) {
+    if (!h || !c) return fail(NRC_B200_ERR_INVALID, "null argument");
+    *c = h->launches;
+    return NRC_B200_OK;
+}
+
+// ---------------------------------------------------------------- parameters
+int nrc_b200_n_params(nrc_b200_handle h, uint32_t* n_params, uint32_t* n_mlp) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (n_params) *n_params = h->n_params;
+    if (n_mlp) *n_mlp = h->n_mlp;
+    return NRC_B200_OK;
+}
+static void* param_ptr(Net* n, int kind, size_t* elem) {
+    switch (kind) {
+        case NRC_B200_PARAMS_MASTER_F32: *elem = 4; return n->master;
+        case NRC_B200_PARAMS_TRAIN_F16: *elem = 2; return n->params;
+        case NRC_B200_PARAMS_EMA_F16: *elem = 2; return n->ema;
+        case NRC_B200_PARAMS_GRAD_F16: *elem = 2; return n->grads;
+        case NRC_B200_ADAM_M1_F32: *elem = 4; return n->m1;
+        case NRC_B200_ADAM_M2_F32: *elem = 4; return n->m2;
+    }
+    return nullptr;
+}
+int nrc_b200_get_params(nrc_b200_handle h, int kind, void* dst) {
+    if (!h || !dst || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    size_t es; void* p = param_ptr(h, kind, &es);
+    if (!p) return fail(NRC_B200_ERR_INVALID, "unknown parameter kind");
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(dst, p, es * h->n_params, cudaMemcpyDeviceToHost));
+    return NRC_B200_OK;
+}
+int nrc_b200_set_params(nrc_b200_handle h, int kind, const void* src) {
+    if (!h || !src || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    size_t es; void* p = param_ptr(h, kind, &es);
+    if (!p) return fail(NRC_B200_ERR_INVALID, "unknown parameter kind");
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(p, src, es * h->n_params, cudaMemcpyHostToDevice));
+    return NRC_B200_OK;
+}
+int nrc_b200_load_master(nrc_b200_handle h, const float* m) {
+    if (!h || !m || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    return upload_master(h, m);
+}
+
+// ---------------------------------------------------------------- inference
+int nrc_b200_infer(nrc_b200_handle h, const float* q, float* r, uint32_t n, void* cu_stream) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;  // silent no-op, NRCNetwork.cu:66
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (n == 0) return NRC_B200_OK;
+    if (!q || !r) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    CU(launch_infer(h->encoding, q, r, n, h->ema, h->gm, h->num_sms, h->stream));
+    h->launches += 1;
+    return NRC_B200_OK;
+}
+
+// Host buffers: 3-deep pipeline of (pinned copy-in -> H2D -> kernel -> D2H -> copy-out) over chunks.
+int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (n == 0) return NRC_B200_OK;
+    if (!q || !r) return fail(NRC_B200_ERR_INVALID, "null host buffer");
+    const uint32_t want = 1u << 18;  // queries per chunk: 15.7 MB in, 3.1 MB out
+    if (h->host_chunk < want) {
+        for (int i = 0; i < Net::kHostChunks; ++i) {
+            CU(cudaMallocHost(&h->pin_in[i], (size_t)want * 60)); CU(cudaMallocHost(&h->pin_out[i], (size_t)want * 12));
+            CU(cudaMalloc(&h->dev_in[i], (size_t)want * 60)); CU(cudaMalloc(&h->dev_out[i], (size_t)want * 12));
+            CU(cudaStreamCreateWithFlags(&h->hstream[i], cudaStreamNonBlocking));
+            CU(cudaEventCreateWithFlags(&h->hevent[i], cudaEventDisableTiming));
+        }
+        h->host_chunk = want;
+    }
+    CU(cudaStreamSynchronize(h->stream));  // weights written by earlier training on h->stream
+    const uint32_t chunk = h->host_chunk;
+    const uint32_t n_chunks = (n + chunk - 1) / chunk;
+    for (uint32_t c = 0; c < n_chunks + Net::kHostChunks; ++c) {
+        if (c >= Net::kHostChunks) {  // retire chunk c - kHostChunks
+            const uint32_t d = c - Net::kHostChunks, s = d % Net::kHostChunks;
+            if (d < n_chunks) {
+                CU(cudaEventSynchronize(h->hevent[s]));
+                const uint32_t cnt = std::min(chunk, n - d * chunk);
+                memcpy(r + (size_t)d * chunk * 3, h->pin_out[s], (size_t)cnt * 12);
+            }
+        }
+        if (c < n_chunks) {
+            const uint32_t s = c % Net::kHostChunks, cnt = std::min(chunk, n - c * chunk);
+            memcpy(h->pin_in[s], q + (size_t)c * chunk * 15, (size_t)cnt * 60);
+            CU(cudaMemcpyAsync(h->dev_in[s], h->pin_in[s], (size_t)cnt * 60, cudaMemcpyHostToDevice, h->hstream[s]));
+            CU(launch_infer(h->encoding, h->dev_in[s], h->dev_out[s], cnt, h->ema, h->gm, h->num_sms, h->hstream[s]));
+            h->launches += 1;
+            CU(cudaMemcpyAsync(h->pin_out[s], h->dev_out[s], (size_t)cnt * 12, cudaMemcpyDeviceToHost, h->hstream[s]));
+            CU(cudaEventRecord(h->hevent[s], h->hstream[s]));
+        }
+    }
+    return NRC_B200_OK;
+}
+
+// ---------------------------------------------------------------- training
+static TrainBuffers train_buffers(Net* h) {
+    TrainBuffers tb;
+    tb.params = h->params; tb.partials = h->partials; tb.grid_grad = h->grid_grad; tb.loss_partials = h->loss_partials;
+    return tb;
+}
+static OptimState optim_state(Net* h) {
+    OptimState os;
+    os.master = h->master; os.params = h->params; os.ema = h->ema; os.grads = h->grads; os.m1 = h->m1; os.m2 = h->m2;
+    os.steps = h->steps; os.n_params = h->n_params; os.n_mlp = h->n_mlp;
+    os.lr = h->lr; os.beta1 = h->beta1; os.beta2 = h->beta2; os.eps = h->eps; os.l2_reg = h->l2_reg;
+    os.ema_decay = h->ema_decay; os.loss_scale = h->loss_scale;
+    return os;
+}
+
+int nrc_b200_train_grad(nrc_b200_handle h, const float* q, const float* t, uint32_t n_local, uint32_t n_global,
+                        float** grad_d, void* cu_stream) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
+        return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
+    const TrainBuffers tb = train_buffers(h);
+    CU(launch_train_fwd_bwd(h->encoding, q, t, n_local, n_global, tb, h->gm, h->stream));
+    CU(launch_reduce_grads(tb, n_local / 128, h->n_params, h->n_mlp, h->grad_f32, h->loss_d, h->stream));
+    h->launches += 2;
+    h->pending_tiles = n_local / 128;
+    if (grad_d) *grad_d = h->grad_f32;
+    return NRC_B200_OK;
+}
+
+int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (h->pending_tiles == 0) return fail(NRC_B200_ERR_INVALID, "train_apply without a pending gradient");
+    h->step += 1;
+    CU(launch_adam_ema(optim_state(h), h->grad_f32, h->grid_grad, h->step, h->stream));
+    h->launches += 1;
+    h->pending_tiles = 0;
+    if (loss_h) {  // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
+        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        *loss_h = *h->loss_pinned;
+    }
+    return NRC_B200_OK;
+}
+
+int nrc_b200_train(nrc_b200_handle h, const float* q, const float* t, void* cu_stream, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;  // NRCNetwork.cu:43
+    int rc = nrc_b200_train_grad(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, nullptr, cu_stream);
+    if (rc != NRC_B200_OK) return rc;
+    return nrc_b200_train_apply(h, nullptr, loss_h);
+}
+
+int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d) {
+    if (!h || !loss_d || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    *loss_d = h->loss_d;
+    return NRC_B200_OK;
+}

@@ -1,0 +1,137 @@
+// Input encodings of the NRC network, evaluated per query in registers (never written to HBM).
+// Math follows the reference's tiny-cuda-nn kernels ("tcnn/" = 3rdparty/tiny-cuda-nn/include/tiny-cuda-nn):
+//   TriangleWave  tcnn/encodings/triangle_wave.h:61-76
+//   OneBlob       tcnn/encodings/oneblob.h:47-67 (AoS, Frequency config) / :99-127 (SoA, Hash config),
+//                 quartic_cdf tcnn/common_device.h:915-920
+//   Identity+pad  tcnn/encodings/identity.h:59-67 (padding lanes are 1.0)
+//   HashGrid      tcnn/encodings/grid.h:94-169, tcnn/common_device.h:651-707,856-868
+// Feature order = CompositeEncoding row order (composite.h:214-280):
+//   Frequency: [0,36) tri-wave d*12+f | [36,60) one-blob | [60,66) albedos | [66,80) 1.0
+//   Hash     : [0,32) grid level*2+f  | [32,56) one-blob | [56,62) albedos | [62,64) 1.0
+#pragma once
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "sm100_prims.cuh"
+
+namespace nrcb {
+
+// Layout of the multiresolution hash grid (grid.h:692-723), filled by the host (nrc_b200.cu).
+struct GridMeta {
+    uint32_t offset[17];   // cumulative entry offsets (entries of 2 fp16 features)
+    uint32_t resolution[16];
+    float scale[16];
+    uint32_t dense_mask;   // bit l set: level l is indexed densely (res^3 <= table size)
+};
+
+// Wrapped quartic-kernel CDF sum  c(d) + c(d-1) + c(d+1)  with  c(t) = clamp(P(4t) + 0.5, 0, 1).
+// c saturates for |t| >= 1/4, so at most one of the three terms is unsaturated: with k = rint(d), r = d - k
+// the sum is  clamp(k+1, 0, 3) + (|k| <= 1 ? c(r) : 0).  r is exact, so the live term matches the
+// reference's bit for bit; the saturated terms contribute exact integers.
+__device__ __forceinline__ float blob_cdf3(float d) {
+    const float k = rintf(d);
+    const float r = d - k;
+    const float u = r * 4.0f;
+    const float u2 = u * u;
+    const float u4 = u2 * u2;
+    const float inner = fmaf(u4, 0.2f, fmaf(u2, -(2.0f / 3.0f), 1.0f));
+    const float c = __saturatef(fmaf(0.9375f * u, inner, 0.5f));
+    const float cnt = fminf(fmaxf(k + 1.0f, 0.0f), 3.0f);
+    return cnt + (fabsf(k) <= 1.0f ? c : 0.0f);
+}
+
+// 4 bins of one dimension. WRAP_LAST = true: Frequency/AoS path (last bin's right edge = left edge of bin 0
+// plus 1, oneblob.h:60-64); false: Hash/SoA path (right edge evaluated at 1.0, oneblob.h:117-121).
+template <bool WRAP_LAST>
+__device__ __forceinline__ void oneblob4(float x, float (&y)[4]) {
+    const float c0 = blob_cdf3(0.0f - x);
+    const float c1 = blob_cdf3(0.25f - x);
+    const float c2 = blob_cdf3(0.5f - x);
+    const float c3 = blob_cdf3(0.75f - x);
+    const float c4 = WRAP_LAST ? c0 + 1.0f : blob_cdf3(1.0f - x);
+    y[0] = c1 - c0; y[1] = c2 - c1; y[2] = c3 - c2; y[3] = c4 - c3;
+}
+
+__device__ __forceinline__ float triwave(float x, int f) {
+    // scalbnf(x, f-1) is exact, so one fma reproduces  x*2^(f-1) + 0.25 f  with a single rounding
+    const float v = fmaf(x, __int_as_float((126 + f) << 23), 0.25f * (float)f);
+    const float r = v - floorf(v);
+    return fmaf(fabsf(r - 0.5f), 4.0f, -1.0f);
+}
+
+// Frequency config: 15 raw floats -> 80 fp16 features packed as 40 half2 words (lo = even feature).
+__device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t (&e)[40]) {
+    float t[36];
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+#pragma unroll
+        for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave(q[d], f);
+#pragma unroll
+    for (int i = 0; i < 18; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+        float y[4];
+        oneblob4<true>(q[3 + d], y);
+        e[18 + 2 * d] = pack_h2(y[0], y[1]);
+        e[19 + 2 * d] = pack_h2(y[2], y[3]);
+    }
+    e[30] = pack_h2(q[9], q[10]);
+    e[31] = pack_h2(q[11], q[12]);
+    e[32] = pack_h2(q[13], q[14]);
+#pragma unroll
+    for (int i = 33; i < 40; ++i) e[i] = 0x3C003C00u;  // (1.0h, 1.0h)
+}
+
+// One level of the hash grid: trilinear interpolation of half2 features, accumulated with half2 fma
+// exactly like the reference (grid.h:146-163: result = fma((T)weight, grid_val, result)).
+__device__ __forceinline__ uint32_t grid_level(const __half2* __restrict__ table, uint32_t size_mask, uint32_t res,
+                                               float scale, bool dense, float x, float y, float z) {
+    float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
+    uint32_t g[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float fl = floorf(p[d]);
+        g[d] = (uint32_t)(int)fl;
+        p[d] -= fl;
+    }
+    __half2 acc = __float2half2_rn(0.0f);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        float w = 1.0f;
+        uint32_t gl[3];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            if (c & (1 << d)) { w *= p[d]; gl[d] = g[d] + 1; } else { w *= 1.0f - p[d]; gl[d] = g[d]; }
+        }
+        uint32_t idx;
+        if (dense) idx = gl[0] + gl[1] * res + gl[2] * res * res;
+        else idx = gl[0] ^ (gl[1] * 2654435761u) ^ (gl[2] * 805459861u);
+        const __half2 v = __ldg(table + (idx & size_mask));
+        acc = __hfma2(__float2half2_rn(w), v, acc);
+    }
+    return *reinterpret_cast<uint32_t*>(&acc);
+}
+
+// Hash config: 15 raw floats -> 64 fp16 features packed as 32 half2 words. Level tables are powers of two
+// (NRCNetworkConfigs.h:98-104: 16^3 = 4096 entries at level 0, 2^log2_hashmap_size above), so `% size` is a mask.
+__device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2* __restrict__ grid,
+                                            const GridMeta& gm, uint32_t (&e)[32]) {
+#pragma unroll
+    for (int l = 0; l < 16; ++l) {
+        const uint32_t size = gm.offset[l + 1] - gm.offset[l];
+        e[l] = grid_level(grid + gm.offset[l], size - 1, gm.resolution[l], gm.scale[l], (gm.dense_mask >> l) & 1, q[0],
+                          q[1], q[2]);
+    }
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+        float y[4];
+        oneblob4<false>(q[3 + d], y);
+        e[16 + 2 * d] = pack_h2(y[0], y[1]);
+        e[17 + 2 * d] = pack_h2(y[2], y[3]);
+    }
+    e[28] = pack_h2(q[9], q[10]);
+    e[29] = pack_h2(q[11], q[12]);
+    e[30] = pack_h2(q[13], q[14]);
+    e[31] = 0x3C003C00u;
+}
+
+}  // namespace nrcb

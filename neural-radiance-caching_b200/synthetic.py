@@ -1,0 +1,71 @@
+"""Seeded synthetic RadianceQuery / target buffers that stand in for the OptiX path tracer's output.
+
+Shape of the data follows the reference's Cornell scene: hit points on the six walls of a box
+of half-extent 10 scaled by 0.005 (nrc/shaders/hit.cu:597), directions/normals as raw spherical angles
+(theta in [0, pi], phi in (-pi, pi]; nrc/shaders/shader_common.h:320-333), roughness in [0,1]^2, diffuse albedo
+by wall, specular mostly 0.  Record layout = nrc::RadianceQuery (neural_radiance_caching.h:100-118):
+[pos(3) | dir(theta,phi) | normal(theta,phi) | roughness(2) | diffuse(3) | specular(3)]  = 15 float32.
+"""
+import numpy as np
+
+
+def _sph(v):
+    """cartesianToSphericalUnitVector: theta = 2*asin(|v - z|/2), phi = atan2(y, x)."""
+    d = v - np.array([0.0, 0.0, 1.0])
+    theta = 2.0 * np.arcsin(np.clip(0.5 * np.linalg.norm(d, axis=-1), 0.0, 1.0))
+    phi = np.arctan2(v[..., 1], v[..., 0])
+    return theta, phi
+
+
+def cornell_queries(n, seed=1337):
+    """n x 15 float32 queries (C-contiguous)."""
+    rng = np.random.Generator(np.random.Philox(seed))
+    wall = rng.integers(0, 6, n)
+    axis, sign = wall // 2, (wall % 2) * 2.0 - 1.0
+    uv = rng.uniform(-10.0, 10.0, (n, 2))
+    pos = np.empty((n, 3))
+    nrm = np.zeros((n, 3))
+    for a in range(3):
+        m = axis == a
+        o = [i for i in range(3) if i != a]
+        pos[m, a] = sign[m] * 10.0
+        pos[np.ix_(m, o)] = uv[m]
+        nrm[m, a] = -sign[m]
+    # cosine-weighted hemisphere direction about the normal
+    u1, u2 = rng.random(n), rng.random(n)
+    r, ph = np.sqrt(u1), 2.0 * np.pi * u2
+    lx, ly, lz = r * np.cos(ph), r * np.sin(ph), np.sqrt(1.0 - u1)
+    t = np.where(np.abs(nrm[:, [0]]) > 0.5, np.array([[0.0, 1.0, 0.0]]), np.array([[1.0, 0.0, 0.0]]))
+    b1 = np.cross(nrm, t)
+    b1 /= np.linalg.norm(b1, axis=1, keepdims=True)
+    b2 = np.cross(nrm, b1)
+    dirs = lx[:, None] * b1 + ly[:, None] * b2 + lz[:, None] * nrm
+    q = np.empty((n, 15), dtype=np.float32)
+    q[:, 0:3] = pos * 0.005
+    q[:, 3], q[:, 4] = _sph(dirs)
+    q[:, 5], q[:, 6] = _sph(nrm)
+    q[:, 7:9] = rng.random((n, 2))
+    diffuse = np.full((n, 3), 0.8)
+    diffuse[wall == 0] = (0.8, 0.1, 0.1)   # red wall
+    diffuse[wall == 1] = (0.1, 0.8, 0.1)   # green wall
+    q[:, 9:12] = diffuse
+    spec = np.zeros((n, 3))
+    m = rng.random(n) < 0.1
+    spec[m] = rng.random((int(m.sum()), 3))
+    q[:, 12:15] = spec
+    return np.ascontiguousarray(q)
+
+
+def uniform_queries(n, seed=1337):
+    """All 15 inputs ~ U[0,1): the one-blob encoding in its non-degenerate regime."""
+    rng = np.random.Generator(np.random.Philox(seed + 7))
+    return np.ascontiguousarray(rng.random((n, 15), dtype=np.float32))
+
+
+def radiance_targets(q, seed=1337):
+    """Smooth analytic radiance + 1 % multiplicative noise, n x 3 float32, >= 0."""
+    rng = np.random.Generator(np.random.Philox(seed + 13))
+    q = q.astype(np.float64)
+    base = (0.5 + 0.5 * np.cos(40.0 * q[:, 0]) * np.cos(40.0 * q[:, 1])) * (1.0 + q[:, 5] / np.pi)
+    t = q[:, 9:12] * base[:, None] * (1.0 + 0.01 * rng.standard_normal((q.shape[0], 1)))
+    return np.ascontiguousarray(np.maximum(t, 0.0).astype(np.float32))
