@@ -83,7 +83,8 @@ typedef enum nrc_b200_param_kind {
     NRC_B200_PARAMS_EMA_F16 = 2,     /* fp16 EMA = inference weights */
     NRC_B200_PARAMS_GRAD_F16 = 3,    /* fp16 gradient of the last step (loss-scaled by 128) */
     NRC_B200_ADAM_M1_F32 = 4,
-    NRC_B200_ADAM_M2_F32 = 5
+    NRC_B200_ADAM_M2_F32 = 5,
+    NRC_B200_GRAD_F32 = 6            /* fp32 gradient vector of the last train_grad (before the fp16 rounding) */
 } nrc_b200_param_kind;
 int nrc_b200_n_params(nrc_b200_handle h, uint32_t* n_params, uint32_t* n_mlp_params);
 int nrc_b200_get_params(nrc_b200_handle h, int kind, void* dst_host);   /* synchronises the stream */

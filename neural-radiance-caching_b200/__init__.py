@@ -22,7 +22,8 @@ NUM_BATCHES = 4                   # neural_radiance_caching.h:29
 BATCH_SIZE = 16384                # neural_radiance_caching.h:31
 NN_INPUT_DIMS, NN_OUTPUT_DIMS = 15, 3
 
-PARAMS_MASTER_F32, PARAMS_TRAIN_F16, PARAMS_EMA_F16, PARAMS_GRAD_F16, ADAM_M1_F32, ADAM_M2_F32 = range(6)
+PARAMS_MASTER_F32, PARAMS_TRAIN_F16, PARAMS_EMA_F16, PARAMS_GRAD_F16, ADAM_M1_F32, ADAM_M2_F32, GRAD_F32 = range(7)
+_F32_KINDS = (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32, GRAD_F32)
 
 # every symbol include/nrc_b200.h declares (tests check the library exports all of them)
 ABI_SYMBOLS = [
@@ -185,7 +186,7 @@ class Network:
     def get_params(self, kind):
         import numpy as np
         n, _ = self.n_params()
-        dt = np.float32 if kind in (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32) else np.float16
+        dt = np.float32 if kind in _F32_KINDS else np.float16
         out = np.empty(n, dtype=dt)
         _check(lib().nrc_b200_get_params(self._h, kind, out.ctypes.data))
         return out
@@ -193,7 +194,7 @@ class Network:
     def set_params(self, kind, arr):
         import numpy as np
         n, _ = self.n_params()
-        dt = np.float32 if kind in (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32) else np.float16
+        dt = np.float32 if kind in _F32_KINDS else np.float16
         a = np.ascontiguousarray(arr, dtype=dt)
         assert a.size == n
         _check(lib().nrc_b200_set_params(self._h, kind, a.ctypes.data))

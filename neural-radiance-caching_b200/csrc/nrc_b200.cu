@@ -238,6 +238,7 @@ static void* param_ptr(Net* n, int kind, size_t* elem) {
         case NRC_B200_PARAMS_GRAD_F16: *elem = 2; return n->grads;
         case NRC_B200_ADAM_M1_F32: *elem = 4; return n->m1;
         case NRC_B200_ADAM_M2_F32: *elem = 4; return n->m2;
+        case NRC_B200_GRAD_F32: *elem = 4; return n->grad_f32;
     }
     return nullptr;
 }
