@@ -64,8 +64,13 @@ int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr);
 int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr);
 
 /* ---- additions without a reference counterpart ------------------------------------------------------ */
-/* Host-buffer query: pinned staging + chunked H2D / kernel / D2H pipeline inside the call (synchronous). */
+/* Host-buffer query: chunked H2D / kernel / D2H pipeline inside the call (synchronous).  Page-locked caller
+ * buffers are DMA'd directly; pageable ones are staged through an internal pinned ring. */
 int nrc_b200_infer_host(nrc_b200_handle h, const float* queries_h, float* radiance_h, uint32_t n);
+/* Host-buffer training step (one batch of 16384): H2D on the training stream, then nrc_b200_train.  Asynchronous
+ * unless loss_h != NULL; the host buffers must stay valid until the stream has consumed them (pinned memory
+ * makes the copies truly asynchronous). */
+int nrc_b200_train_host(nrc_b200_handle h, const float* queries_h, const float* targets_h, float* loss_h);
 /* Device-side loss of the most recent train() call, without forcing a sync on the training stream. */
 int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d);
 

@@ -29,7 +29,7 @@ _F32_KINDS = (PARAMS_MASTER_F32, ADAM_M1_F32, ADAM_M2_F32, GRAD_F32)
 ABI_SYMBOLS = [
     "nrc_b200_create", "nrc_b200_create_ex", "nrc_b200_destroy", "nrc_b200_reset", "nrc_b200_infer",
     "nrc_b200_train", "nrc_b200_set_stream", "nrc_b200_set_learning_rate", "nrc_b200_get_learning_rate",
-    "nrc_b200_infer_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
+    "nrc_b200_infer_host", "nrc_b200_train_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
     "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
     "nrc_b200_last_error", "nrc_b200_launch_count",
 ]
@@ -67,6 +67,7 @@ def lib():
         L.nrc_b200_set_learning_rate.argtypes = [vp, f32]
         L.nrc_b200_get_learning_rate.argtypes = [vp, P(f32)]
         L.nrc_b200_infer_host.argtypes = [vp, vp, vp, u32]
+        L.nrc_b200_train_host.argtypes = [vp, vp, vp, P(f32)]
         L.nrc_b200_last_loss_device.argtypes = [vp, P(vp)]
         L.nrc_b200_train_grad.argtypes = [vp, vp, vp, u32, u32, P(vp), vp]
         L.nrc_b200_train_apply.argtypes = [vp, vp, P(f32)]
@@ -160,6 +161,12 @@ class Network:
     # ---- additions (no reference counterpart) ---------------------------------------------------------
     def infer_host(self, inputs_h, outputs_h, numInputs):
         _check(lib().nrc_b200_infer_host(self._h, _ptr(inputs_h), _ptr(outputs_h), int(numInputs)))
+
+    def train_host(self, inputs_h, targets_h, want_loss=False):
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train_host(self._h, _ptr(inputs_h), _ptr(targets_h),
+                                         ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
 
     def train_grad(self, inputs_d, targets_d, n_local, n_global, stream=None):
         """Gradient of this rank's shard; returns the device pointer of the fp32 gradient (n_params floats)."""

@@ -48,6 +48,7 @@ struct nrc_b200_network {
     float* dev_in[kHostChunks] = {}; float* dev_out[kHostChunks] = {};
     cudaStream_t hstream[kHostChunks] = {}; cudaEvent_t hevent[kHostChunks] = {};
     uint32_t host_chunk = 0;
+    float* train_in_d = nullptr; float* train_tgt_d = nullptr;   // staging for train_host (one 16384 batch)
     uint64_t launches = 0;
     bool destroyed = false;
 };
@@ -107,6 +108,8 @@ static void free_all(Net* n) {
         n->hstream[i] = nullptr; n->hevent[i] = nullptr;
     }
     n->host_chunk = 0;
+    cudaFree(n->train_in_d); cudaFree(n->train_tgt_d);
+    n->train_in_d = n->train_tgt_d = nullptr;
 }
 
 // Uploads fp32 master weights, derives the fp16 copy (trainer.h:83-86), zeroes EMA (ema.h:93-94) and Adam state.
@@ -275,6 +278,12 @@ int nrc_b200_infer(nrc_b200_handle h, const float* q, float* r, uint32_t n, void
     return NRC_B200_OK;
 }
 
+static bool is_pinned_host(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
 // Host buffers: 3-deep pipeline of (pinned copy-in -> H2D -> kernel -> D2H -> copy-out) over chunks.
 int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
@@ -292,6 +301,9 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
         h->host_chunk = want;
     }
     CU(cudaStreamSynchronize(h->stream));  // weights written by earlier training on h->stream
+    // Page-locked caller buffers (cudaHostAlloc / cudaHostRegister) are DMA'd directly; pageable ones go through
+    // the pinned staging ring.
+    const bool q_pinned = is_pinned_host(q), r_pinned = is_pinned_host(r);
     const uint32_t chunk = h->host_chunk;
     const uint32_t n_chunks = (n + chunk - 1) / chunk;
     for (uint32_t c = 0; c < n_chunks + Net::kHostChunks; ++c) {
@@ -300,16 +312,18 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
             if (d < n_chunks) {
                 CU(cudaEventSynchronize(h->hevent[s]));
                 const uint32_t cnt = std::min(chunk, n - d * chunk);
-                memcpy(r + (size_t)d * chunk * 3, h->pin_out[s], (size_t)cnt * 12);
+                if (!r_pinned) memcpy(r + (size_t)d * chunk * 3, h->pin_out[s], (size_t)cnt * 12);
             }
         }
         if (c < n_chunks) {
             const uint32_t s = c % Net::kHostChunks, cnt = std::min(chunk, n - c * chunk);
-            memcpy(h->pin_in[s], q + (size_t)c * chunk * 15, (size_t)cnt * 60);
-            CU(cudaMemcpyAsync(h->dev_in[s], h->pin_in[s], (size_t)cnt * 60, cudaMemcpyHostToDevice, h->hstream[s]));
+            const float* src = q + (size_t)c * chunk * 15;
+            if (!q_pinned) { memcpy(h->pin_in[s], src, (size_t)cnt * 60); src = h->pin_in[s]; }
+            CU(cudaMemcpyAsync(h->dev_in[s], src, (size_t)cnt * 60, cudaMemcpyHostToDevice, h->hstream[s]));
             CU(launch_infer(h->encoding, h->dev_in[s], h->dev_out[s], cnt, h->ema, h->gm, h->num_sms, h->hstream[s]));
             h->launches += 1;
-            CU(cudaMemcpyAsync(h->pin_out[s], h->dev_out[s], (size_t)cnt * 12, cudaMemcpyDeviceToHost, h->hstream[s]));
+            float* dst = r_pinned ? r + (size_t)c * chunk * 3 : h->pin_out[s];
+            CU(cudaMemcpyAsync(dst, h->dev_out[s], (size_t)cnt * 12, cudaMemcpyDeviceToHost, h->hstream[s]));
             CU(cudaEventRecord(h->hevent[s], h->hstream[s]));
         }
     }
@@ -371,6 +385,20 @@ int nrc_b200_train(nrc_b200_handle h, const float* q, const float* t, void* cu_s
     int rc = nrc_b200_train_grad(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, nullptr, cu_stream);
     if (rc != NRC_B200_OK) return rc;
     return nrc_b200_train_apply(h, nullptr, loss_h);
+}
+
+// Host-buffer training step: H2D of one batch (983 KB + 197 KB) on the training stream, then the same kernels.
+int nrc_b200_train_host(nrc_b200_handle h, const float* q_h, const float* t_h, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (!q_h || !t_h) return fail(NRC_B200_ERR_INVALID, "null host buffer");
+    if (!h->train_in_d) {
+        CU(cudaMalloc(&h->train_in_d, (size_t)NRC_B200_BATCH_SIZE * 60));
+        CU(cudaMalloc(&h->train_tgt_d, (size_t)NRC_B200_BATCH_SIZE * 12));
+    }
+    CU(cudaMemcpyAsync(h->train_in_d, q_h, (size_t)NRC_B200_BATCH_SIZE * 60, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->train_tgt_d, t_h, (size_t)NRC_B200_BATCH_SIZE * 12, cudaMemcpyHostToDevice, h->stream));
+    return nrc_b200_train(h, h->train_in_d, h->train_tgt_d, nullptr, loss_h);
 }
 
 int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d) {

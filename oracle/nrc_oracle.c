@@ -9,7 +9,18 @@
 typedef _Float16 h16;
 
 uint16_t nrc_oracle_f2h(float f) { h16 h = (h16)f; uint16_t u; memcpy(&u, &h, 2); return u; }
-float nrc_oracle_h2f(uint16_t u) { h16 h; memcpy(&h, &u, 2); return (float)h; }
+/* fp16 -> fp32 is exact; a 65536-entry table keeps the scalar baseline from paying a soft-float call per weight. */
+static float g_h2f[65536];
+__attribute__((constructor)) static void init_h2f(void) {
+    for (uint32_t u = 0; u < 65536; ++u) { uint16_t v = (uint16_t)u; h16 h; memcpy(&h, &v, 2); g_h2f[u] = (float)h; }
+}
+float nrc_oracle_h2f(uint16_t u) { return g_h2f[u]; }
+/* MLP weights widened to fp32 once per call (exact), so the inner loops are plain float MACs. */
+static float* widen_weights(const uint16_t* P, int n) {
+    float* w = (float*)malloc((size_t)n * sizeof(float));
+    for (int i = 0; i < n; ++i) w[i] = g_h2f[P[i]];
+    return w;
+}
 static inline float rh(float f) { return (float)(h16)f; } /* round through fp16 */
 
 /* ---------------------------------------------------------------- model layout */
@@ -165,16 +176,16 @@ void nrc_oracle_encode(const nrc_oracle_spec* s, const uint16_t* params_h, const
 /* Semantics of kernel_mlp_fused (tcnn/src/fully_fused_mlp.cu:47-129,422-476,499-557): six bias-free matrices
  * W[out][in] row-major (fully_fused_mlp.cu:854-863), ReLU after every layer including the output
  * (NRCNetworkConfigs.h:26-33), every layer's activations stored as fp16. */
-static void dense_relu(const uint16_t* W, int n_out, int n_in, const float* x, float* y, int acc_mode) {
+static void dense_relu(const float* W, int n_out, int n_in, const float* x, float* y, int acc_mode) {
     for (int o = 0; o < n_out; ++o) {
-        const uint16_t* w = W + (size_t)o * n_in;
+        const float* w = W + (size_t)o * n_in;
         float acc = 0;
         if (acc_mode == 0) {
-            for (int k = 0; k < n_in; ++k) acc += nrc_oracle_h2f(w[k]) * x[k];
+            for (int k = 0; k < n_in; ++k) acc += w[k] * x[k];
         } else { /* accumulator kept in fp16 between 16-wide k blocks (wmma accumulator<__half>, :68) */
             for (int kb = 0; kb < n_in; kb += 16) {
                 float blk = 0;
-                for (int k = kb; k < kb + 16; ++k) blk += nrc_oracle_h2f(w[k]) * x[k];
+                for (int k = kb; k < kb + 16; ++k) blk += w[k] * x[k];
                 acc = rh(acc + blk);
             }
         }
@@ -183,12 +194,13 @@ static void dense_relu(const uint16_t* W, int n_out, int n_in, const float* x, f
 }
 
 /* acts: [x(E) | h1..h5 (5x64) | y(16)] as floats holding fp16 values */
-static void forward_one(const nrc_oracle_spec* s, const uint16_t* P, const float* q, float* acts, int acc_mode) {
+static void forward_one(const nrc_oracle_spec* s, const uint16_t* P, const float* Wf, const float* q, float* acts,
+                        int acc_mode) {
     const int E = s->enc_width;
     uint16_t e[80];
     encode_one(s, P, q, e);
     for (int i = 0; i < E; ++i) acts[i] = nrc_oracle_h2f(e[i]);
-    const uint16_t* W = P;
+    const float* W = Wf;
     dense_relu(W, 64, E, acts, acts + E, acc_mode);
     W += 64 * E;
     for (int l = 0; l < 4; ++l) {
@@ -199,13 +211,13 @@ static void forward_one(const nrc_oracle_spec* s, const uint16_t* P, const float
 }
 
 typedef struct {
-    const nrc_oracle_spec* s; const uint16_t* P; const float* in; float* out; uint32_t lo, hi; int acc_mode;
+    const nrc_oracle_spec* s; const uint16_t* P; const float* Wf; const float* in; float* out; uint32_t lo, hi; int acc_mode;
 } infer_job;
 static void* infer_worker(void* a) {
     infer_job* j = (infer_job*)a;
     float acts[80 + 5 * 64 + 16];
     for (uint32_t i = j->lo; i < j->hi; ++i) {
-        forward_one(j->s, j->P, j->in + (size_t)i * 15, acts, j->acc_mode);
+        forward_one(j->s, j->P, j->Wf, j->in + (size_t)i * 15, acts, j->acc_mode);
         const float* y = acts + j->s->enc_width + 5 * 64;
         /* trim_and_cast: common_device.h:990-999 (first 3 of 16 lanes -> f32) */
         for (int c = 0; c < 3; ++c) j->out[(size_t)i * 3 + c] = y[c];
@@ -221,18 +233,20 @@ void nrc_oracle_infer(const nrc_oracle_spec* s, const uint16_t* params_h, const 
     if (nthreads > 256) nthreads = 256;
     pthread_t th[256];
     infer_job jobs[256];
+    float* Wf = widen_weights(params_h, s->n_mlp_params);
     for (int t = 0; t < nthreads; ++t) {
-        jobs[t] = (infer_job){s, params_h, in, out, (uint32_t)((uint64_t)n * t / nthreads),
+        jobs[t] = (infer_job){s, params_h, Wf, in, out, (uint32_t)((uint64_t)n * t / nthreads),
                               (uint32_t)((uint64_t)n * (t + 1) / nthreads), acc_mode};
         if (nthreads == 1) infer_worker(&jobs[t]);
         else pthread_create(&th[t], 0, infer_worker, &jobs[t]);
     }
     if (nthreads > 1) for (int t = 0; t < nthreads; ++t) pthread_join(th[t], 0);
+    free(Wf);
 }
 
 /* ---------------------------------------------------------------- training */
 typedef struct {
-    nrc_oracle_state* st; const float* in; const float* tgt; uint32_t lo, hi, n_norm;
+    nrc_oracle_state* st; const float* Wf; const float* in; const float* tgt; uint32_t lo, hi, n_norm;
     double* gw;   /* [n_mlp_params] partial weight gradients (loss-scaled)    */
     float* gg;    /* [n_grid_params] partial grid gradients (Hash) or NULL    */
     double loss;
@@ -251,7 +265,7 @@ static void* grad_worker(void* a) {
     float acts[80 + 5 * 64 + 16], g[16], d[5][64], dx[64];
     for (uint32_t i = j->lo; i < j->hi; ++i) {
         const float* q = j->in + (size_t)i * 15;
-        forward_one(s, P, q, acts, 0);
+        forward_one(s, P, j->Wf, q, acts, 0);
         const float* x = acts;
         const float* h = acts + E; /* h[l*64 + k], l = 0..4 */
         const float* y = acts + E + 5 * 64;
@@ -266,17 +280,17 @@ static void* grad_worker(void* a) {
             g[c] = rh(gh * (y[c] > 0 ? 1.0f : 0.0f));
         }
         /* delta_5 = (W_out^T g) .* [h5 > 0] */
-        const uint16_t* Wout = P + 64 * E + 4 * 4096;
+        const float* Wout = j->Wf + 64 * E + 4 * 4096;
         for (int k = 0; k < 64; ++k) {
             float acc = 0;
-            for (int c = 0; c < 16; ++c) acc += nrc_oracle_h2f(Wout[c * 64 + k]) * g[c];
+            for (int c = 0; c < 16; ++c) acc += Wout[c * 64 + k] * g[c];
             d[4][k] = rh(h[4 * 64 + k] > 0 ? acc : 0.0f);
         }
         for (int l = 3; l >= 0; --l) { /* delta_l = (W_h(l+1)^T delta_(l+1)) .* [h_l > 0] */
-            const uint16_t* W = P + 64 * E + l * 4096;
+            const float* W = j->Wf + 64 * E + l * 4096;
             for (int k = 0; k < 64; ++k) {
                 float acc = 0;
-                for (int o = 0; o < 64; ++o) acc += nrc_oracle_h2f(W[o * 64 + k]) * d[l + 1][o];
+                for (int o = 0; o < 64; ++o) acc += W[o * 64 + k] * d[l + 1][o];
                 d[l][k] = rh(h[l * 64 + k] > 0 ? acc : 0.0f);
             }
         }
@@ -299,7 +313,7 @@ static void* grad_worker(void* a) {
         if (j->gg) { /* Hash: dL/d(encoded) = W_in^T delta_1 (fp16), rows 0..31, then scatter to the 8 corners */
             for (int k = 0; k < 32; ++k) {
                 float acc = 0;
-                for (int o = 0; o < 64; ++o) acc += nrc_oracle_h2f(P[o * E + k]) * d[0][o];
+                for (int o = 0; o < 64; ++o) acc += j->Wf[o * E + k] * d[0][o];
                 dx[k] = rh(acc);
             }
             for (uint32_t level = 0; level < 16; ++level) {
@@ -339,8 +353,9 @@ float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* t
     if ((uint32_t)nthreads > n) nthreads = n ? (int)n : 1;
     pthread_t th[64];
     grad_job jobs[64];
+    float* Wf = widen_weights(st->params, s->n_mlp_params);
     for (int t = 0; t < nthreads; ++t) {
-        jobs[t] = (grad_job){st, in, targets, (uint32_t)((uint64_t)n * t / nthreads),
+        jobs[t] = (grad_job){st, Wf, in, targets, (uint32_t)((uint64_t)n * t / nthreads),
                              (uint32_t)((uint64_t)n * (t + 1) / nthreads), n_norm,
                              (double*)calloc(s->n_mlp_params, sizeof(double)),
                              s->n_grid_params ? (float*)calloc(s->n_grid_params, sizeof(float)) : 0, 0.0};
@@ -356,6 +371,7 @@ float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* t
         grad_accum[i] += (float)acc;
     }
     for (int t = 0; t < nthreads; ++t) { loss += jobs[t].loss; free(jobs[t].gw); free(jobs[t].gg); }
+    free(Wf);
     return (float)loss;
 }
 
