@@ -42,13 +42,15 @@ int nrc_ref_train(void* h, float* in_d, float* tgt_d, void* stream, float* loss_
 }
 int nrc_ref_set_lr(void* h, float lr) { GUARD(((nrc::Network*)h)->setHyperParams(nrc::HyperParams{lr})) }
 int nrc_ref_n_params(void* h) { return (int)((nrc::Network*)h)->pImpl->model.trainer->n_params(); }
-// which: 0 = fp32 master, 1 = fp16 training weights, 2 = fp16 inference (EMA) weights; host buffers
+// which: 0 = fp32 master, 1 = fp16 training weights, 2 = fp16 inference (EMA) weights,
+//        3 = fp16 gradients of the last step (loss-scaled by 128); host buffers
 int nrc_ref_get_params(void* h, int which, void* dst_h) {
     GUARD({
         auto& t = ((nrc::Network*)h)->pImpl->model.trainer;
         size_t n = t->n_params();
         const void* src = which == 0 ? (const void*)t->params_full_precision()
-                        : which == 1 ? (const void*)t->params() : (const void*)t->params_inference();
+                        : which == 1 ? (const void*)t->params()
+                        : which == 2 ? (const void*)t->params_inference() : (const void*)t->param_gradients();
         CUDA_CHECK_THROW(cudaDeviceSynchronize());
         CUDA_CHECK_THROW(cudaMemcpy(dst_h, src, n * (which == 0 ? 4 : 2), cudaMemcpyDeviceToHost));
     })
