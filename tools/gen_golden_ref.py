@@ -64,20 +64,29 @@ def main():
                             grad_grid_abs_sum=np.float64(np.abs(g[n_mlp:].astype(np.float64)).sum()))
         net.destroy()
 
-        # ---------------- loss curve over n_steps from the seeded init (grid at its U(-1e-4,1e-4)-like init)
-        net = ref_gpu.RefNetwork(enc, 0)
-        master = gu.seeded_master(enc, net.n, visible_grid=False)
-        net.set_master(master)
-        losses = np.zeros(n_steps, dtype=np.float32)
-        for s in range(n_steps):
-            qs, ts = gu.batch(s)
-            qs_d, ts_d = torch.from_numpy(qs).cuda(), torch.from_numpy(ts).cuda()
-            losses[s] = net.train(qs_d.data_ptr(), ts_d.data_ptr(), want_loss=True)
-        net.infer(q_d.data_ptr(), o_d.data_ptr(), q.shape[0])
-        torch.cuda.synchronize()
-        extra = {"ema": net.get_params(2)} if enc == 0 else {}
-        np.savez_compressed(os.path.join(out_dir, f"ref_curve_{name}.npz"), losses=losses, radiance=o_d.cpu().numpy(), **extra)
-        net.destroy()
+        # ---------------- loss curve over n_steps from the seeded init (grid at its U(-1e-4,1e-4)-like init).
+        # Run twice: the Hash config scatters gradients with fp16 atomics (grid.h:301-319), so the reference is
+        # not reproducible run to run; `losses_rerun` lets the tests scale their tolerance by the reference's own spread.
+        curves = []
+        for rerun in range(2):
+            net = ref_gpu.RefNetwork(enc, 0)
+            master = gu.seeded_master(enc, net.n, visible_grid=False)
+            net.set_master(master)
+            losses = np.zeros(n_steps, dtype=np.float32)
+            for s in range(n_steps):
+                qs, ts = gu.batch(s)
+                qs_d, ts_d = torch.from_numpy(qs).cuda(), torch.from_numpy(ts).cuda()
+                losses[s] = net.train(qs_d.data_ptr(), ts_d.data_ptr(), want_loss=True)
+            curves.append(losses)
+            if rerun == 0:
+                net.infer(q_d.data_ptr(), o_d.data_ptr(), q.shape[0])
+                torch.cuda.synchronize()
+                radiance = o_d.cpu().numpy()
+                extra = {"ema": net.get_params(2)} if enc == 0 else {}
+            net.destroy()
+        losses = curves[0]
+        np.savez_compressed(os.path.join(out_dir, f"ref_curve_{name}.npz"), losses=curves[0], losses_rerun=curves[1],
+                            radiance=radiance, **extra)
         print(name, "loss1", loss1, "curve", losses[:3], losses[-3:])
 
 
