@@ -97,6 +97,9 @@ int nrc_b200_set_params(nrc_b200_handle h, int kind, const void* src_host);
 /* Loads fp32 master weights, derives the fp16 training copy, zeroes EMA/Adam state and the step counter. */
 int nrc_b200_load_master(nrc_b200_handle h, const float* master_host);
 
+/* Debug aid: per-tile clock64 phase stamps of the training step kernel ([128][8] int64; see csrc/nrc_b200.cu). */
+int nrc_b200_debug_train_timeline(nrc_b200_handle h, int enable, long long* dst_host);
+
 const char* nrc_b200_last_error(void);
 /* Number of kernel launches issued through this handle so far (bench.py's gpu_launches). */
 int nrc_b200_launch_count(nrc_b200_handle h, uint64_t* count);

@@ -31,7 +31,7 @@ ABI_SYMBOLS = [
     "nrc_b200_train", "nrc_b200_set_stream", "nrc_b200_set_learning_rate", "nrc_b200_get_learning_rate",
     "nrc_b200_infer_host", "nrc_b200_train_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
     "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
-    "nrc_b200_last_error", "nrc_b200_launch_count",
+    "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline",
 ]
 
 
@@ -77,6 +77,7 @@ def lib():
         L.nrc_b200_load_master.argtypes = [vp, vp]
         L.nrc_b200_last_error.restype = ctypes.c_char_p
         L.nrc_b200_launch_count.argtypes = [vp, P(u64)]
+        L.nrc_b200_debug_train_timeline.argtypes = [vp, i32, vp]
         _lib = L
     return _lib
 
@@ -211,6 +212,12 @@ class Network:
         a = np.ascontiguousarray(master, dtype=np.float32)
         assert a.size == self.n_params()[0]
         _check(lib().nrc_b200_load_master(self._h, a.ctypes.data))
+
+    def debug_train_timeline(self, enable=True, read=False):
+        import numpy as np
+        out = np.zeros((128, 8), dtype=np.int64) if read else None
+        _check(lib().nrc_b200_debug_train_timeline(self._h, int(enable), out.ctypes.data if read else None))
+        return out
 
     def launch_count(self):
         c = ctypes.c_uint64()

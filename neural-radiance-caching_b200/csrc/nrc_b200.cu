@@ -33,6 +33,9 @@ struct nrc_b200_network {
     GridMeta gm{};
     // parameter block (device)
     float* master = nullptr; __half* params = nullptr; __half* ema = nullptr; __half* grads = nullptr;
+    __half* params_img = nullptr;   // UMMA shared-memory image of the fp16 training MLP weights (bulk-copied by the step kernel)
+    uint32_t* barrier_counter = nullptr; uint32_t barrier_total = 0;
+    long long* timeline = nullptr;   // debug: per-tile phase stamps of the step kernel   // grid barrier of the cooperative step kernel
     float* m1 = nullptr; float* m2 = nullptr; uint32_t* steps = nullptr;
     // training scratch (device)
     float* partials = nullptr; float* grid_grad = nullptr; float* loss_partials = nullptr;
@@ -92,7 +95,9 @@ static float u01(uint64_t& s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16
 
 static void free_all(Net* n) {
     cudaFree(n->master); cudaFree(n->params); cudaFree(n->ema); cudaFree(n->grads);
-    cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps);
+    cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps); cudaFree(n->params_img); cudaFree(n->barrier_counter);
+    n->params_img = nullptr; n->barrier_counter = nullptr; n->barrier_total = 0;
+    cudaFree(n->timeline); n->timeline = nullptr;
     cudaFree(n->partials); cudaFree(n->grid_grad); cudaFree(n->loss_partials); cudaFree(n->grad_f32); cudaFree(n->loss_d);
     if (n->loss_pinned) cudaFreeHost(n->loss_pinned);
     n->master = nullptr; n->params = nullptr; n->ema = nullptr; n->grads = nullptr; n->m1 = n->m2 = nullptr;
@@ -126,6 +131,7 @@ static int upload_master(Net* n, const float* host_master) {
     CU(cudaMemsetAsync(n->grad_f32, 0, (size_t)n->n_params * 4, n->stream));
     if (n->grid_grad) CU(cudaMemsetAsync(n->grid_grad, 0, (size_t)(n->n_params - n->n_mlp) * 4, n->stream));
     CU(cudaMemsetAsync(n->loss_d, 0, 4, n->stream));
+    CU(launch_make_image(n->params, n->params_img, n->enc_width, n->n_mlp, n->stream));
     CU(cudaStreamSynchronize(n->stream));  // host vectors go out of scope
     n->step = 0;
     n->pending_tiles = 0;
@@ -143,6 +149,10 @@ static int build_model(Net* n) {
     CU(cudaMalloc(&n->master, P * 4)); CU(cudaMalloc(&n->params, P * 2)); CU(cudaMalloc(&n->ema, P * 2));
     CU(cudaMalloc(&n->grads, P * 2)); CU(cudaMalloc(&n->m1, P * 4)); CU(cudaMalloc(&n->m2, P * 4));
     CU(cudaMalloc(&n->steps, P * 4)); CU(cudaMalloc(&n->grad_f32, P * 4));
+    CU(cudaMalloc(&n->params_img, (size_t)n->n_mlp * 2));
+    CU(cudaMalloc(&n->barrier_counter, 4));
+    CU(cudaMemset(n->barrier_counter, 0, 4));
+    n->barrier_total = 0;
     CU(cudaMalloc(&n->partials, (size_t)kMaxTrainTiles * n->n_mlp * 4));
     CU(cudaMalloc(&n->loss_partials, kMaxTrainTiles * 4));
     CU(cudaMalloc(&n->loss_d, 4));
@@ -259,6 +269,10 @@ int nrc_b200_set_params(nrc_b200_handle h, int kind, const void* src) {
     if (!p) return fail(NRC_B200_ERR_INVALID, "unknown parameter kind");
     CU(cudaStreamSynchronize(h->stream));
     CU(cudaMemcpy(p, src, es * h->n_params, cudaMemcpyHostToDevice));
+    if (kind == NRC_B200_PARAMS_TRAIN_F16) {
+        CU(launch_make_image(h->params, h->params_img, h->enc_width, h->n_mlp, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
     return NRC_B200_OK;
 }
 int nrc_b200_load_master(nrc_b200_handle h, const float* m) {
@@ -331,18 +345,23 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
 }
 
 // ---------------------------------------------------------------- training
-static TrainBuffers train_buffers(Net* h) {
-    TrainBuffers tb;
-    tb.params = h->params; tb.partials = h->partials; tb.grid_grad = h->grid_grad; tb.loss_partials = h->loss_partials;
-    return tb;
-}
-static OptimState optim_state(Net* h) {
-    OptimState os;
-    os.master = h->master; os.params = h->params; os.ema = h->ema; os.grads = h->grads; os.m1 = h->m1; os.m2 = h->m2;
-    os.steps = h->steps; os.n_params = h->n_params; os.n_mlp = h->n_mlp;
-    os.lr = h->lr; os.beta1 = h->beta1; os.beta2 = h->beta2; os.eps = h->eps; os.l2_reg = h->l2_reg;
-    os.ema_decay = h->ema_decay; os.loss_scale = h->loss_scale;
-    return os;
+static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_local, uint32_t n_global, int apply) {
+    TrainArgs a{};
+    a.in = q; a.targets = t; a.n_local = n_local; a.n_global = n_global;
+    a.master = h->master; a.params = h->params; a.params_img = h->params_img; a.ema = h->ema; a.grads = h->grads;
+    a.m1 = h->m1; a.m2 = h->m2; a.steps = h->steps;
+    a.partials = h->partials; a.grid_grad = h->grid_grad; a.loss_partials = h->loss_partials;
+    a.grad_f32 = h->grad_f32; a.loss_out = h->loss_d;
+    a.barrier_counter = h->barrier_counter; a.barrier_target = h->barrier_total;
+    a.n_params = h->n_params; a.n_mlp = h->n_mlp;
+    a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
+    a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
+    // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double; h->step is the step being applied
+    a.ema_debias_old = 1.0f - (float)pow((double)h->ema_decay, (double)(h->step - 1));
+    a.ema_debias_new = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)h->step));
+    a.apply = apply;
+    a.timeline = h->timeline;
+    return a;
 }
 
 int nrc_b200_train_grad(nrc_b200_handle h, const float* q, const float* t, uint32_t n_local, uint32_t n_global,
@@ -353,10 +372,9 @@ int nrc_b200_train_grad(nrc_b200_handle h, const float* q, const float* t, uint3
     if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
     if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
         return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
-    const TrainBuffers tb = train_buffers(h);
-    CU(launch_train_fwd_bwd(h->encoding, q, t, n_local, n_global, tb, h->gm, h->stream));
-    CU(launch_reduce_grads(tb, n_local / 128, h->n_params, h->n_mlp, h->grad_f32, h->loss_d, h->stream));
-    h->launches += 2;
+    h->barrier_total += n_local / 128;
+    CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/0), h->gm, h->stream));
+    h->launches += 1;
     h->pending_tiles = n_local / 128;
     if (grad_d) *grad_d = h->grad_f32;
     return NRC_B200_OK;
@@ -368,7 +386,7 @@ int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h) {
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (h->pending_tiles == 0) return fail(NRC_B200_ERR_INVALID, "train_apply without a pending gradient");
     h->step += 1;
-    CU(launch_adam_ema(optim_state(h), h->grad_f32, h->grid_grad, h->step, h->stream));
+    CU(launch_adam_ema(train_args(h, nullptr, nullptr, 0, 0, 1), h->stream));
     h->launches += 1;
     h->pending_tiles = 0;
     if (loss_h) {  // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
@@ -382,9 +400,20 @@ int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h) {
 int nrc_b200_train(nrc_b200_handle h, const float* q, const float* t, void* cu_stream, float* loss_h) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
     if (h->destroyed) return NRC_B200_ERR_DESTROYED;  // NRCNetwork.cu:43
-    int rc = nrc_b200_train_grad(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, nullptr, cu_stream);
-    if (rc != NRC_B200_OK) return rc;
-    return nrc_b200_train_apply(h, nullptr, loss_h);
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    // one cooperative launch: forward + loss + backward + gradient reduction + Adam + EMA
+    h->step += 1;
+    h->barrier_total += NRC_B200_BATCH_SIZE / 128;
+    CU(launch_train_step(h->encoding, train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1), h->gm, h->stream));
+    h->launches += 1;
+    h->pending_tiles = 0;
+    if (loss_h) {  // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
+        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        *loss_h = *h->loss_pinned;
+    }
+    return NRC_B200_OK;
 }
 
 // Host-buffer training step: H2D of one batch (983 KB + 197 KB) on the training stream, then the same kernels.
@@ -399,6 +428,22 @@ int nrc_b200_train_host(nrc_b200_handle h, const float* q_h, const float* t_h, f
     CU(cudaMemcpyAsync(h->train_in_d, q_h, (size_t)NRC_B200_BATCH_SIZE * 60, cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemcpyAsync(h->train_tgt_d, t_h, (size_t)NRC_B200_BATCH_SIZE * 12, cudaMemcpyHostToDevice, h->stream));
     return nrc_b200_train(h, h->train_in_d, h->train_tgt_d, nullptr, loss_h);
+}
+
+// Debug: per-tile clock64 stamps of the last training step [128 tiles][8 slots]:
+// 0 start, 1 encoded, 2 forward done, 3 backward + weight gradients done, 4 partials stored, 5 past the grid barrier, 6 end.
+int nrc_b200_debug_train_timeline(nrc_b200_handle h, int enable, long long* dst_host) {
+    if (!h || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle");
+    if (enable && !h->timeline) {
+        CU(cudaMalloc(&h->timeline, 128 * 8 * sizeof(long long)));
+        CU(cudaMemset(h->timeline, 0, 128 * 8 * sizeof(long long)));
+    }
+    if (dst_host && h->timeline) {
+        CU(cudaStreamSynchronize(h->stream));
+        CU(cudaMemcpy(dst_host, h->timeline, 128 * 8 * sizeof(long long), cudaMemcpyDeviceToHost));
+    }
+    if (!enable && h->timeline) { CU(cudaStreamSynchronize(h->stream)); cudaFree(h->timeline); h->timeline = nullptr; }
+    return NRC_B200_OK;
 }
 
 int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d) {

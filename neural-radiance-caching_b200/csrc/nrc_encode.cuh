@@ -30,13 +30,14 @@ struct GridMeta {
 __device__ __forceinline__ float blob_cdf3(float d) {
     const float k = rintf(d);
     const float r = d - k;
-    const float u = r * 4.0f;
-    const float u2 = u * u;
-    const float u4 = u2 * u2;
-    const float inner = fmaf(u4, 0.2f, fmaf(u2, -(2.0f / 3.0f), 1.0f));
-    const float c = __saturatef(fmaf(0.9375f * u, inner, 0.5f));
-    const float cnt = fminf(fmaxf(k + 1.0f, 0.0f), 3.0f);
-    return cnt + (fabsf(k) <= 1.0f ? c : 0.0f);
+    // c(r) = sat(15/16 u (1 - 2/3 u^2 + 1/5 u^4) + 1/2), u = 4r.  Powers of two are folded into the constants
+    // (u^2 = 16 r^2, u^4 = 256 r^4, 15/16 u = 3.75 r): every product keeps the reference's rounding exactly.
+    const float q2 = r * r;
+    const float q4 = q2 * q2;
+    const float inner = fmaf(q4, 256.0f * 0.2f, fmaf(q2, 16.0f * -(2.0f / 3.0f), 1.0f));
+    const float c = __saturatef(fmaf(3.75f * r, inner, 0.5f));
+    // clamp(k+1, 0, 3) + (|k| <= 1 ? c : 0)  ==  clamp((k+1) + c, 0, 3):  for |k| >= 2 the sum is already outside [0, 3].
+    return fminf(fmaxf((k + 1.0f) + c, 0.0f), 3.0f);
 }
 
 // 4 bins of one dimension. WRAP_LAST = true: Frequency/AoS path (last bin's right edge = left edge of bin 0
@@ -83,7 +84,10 @@ __device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t 
 
 // One level of the hash grid: trilinear interpolation of half2 features, accumulated with half2 fma
 // exactly like the reference (grid.h:146-163: result = fma((T)weight, grid_val, result)).
-__device__ __forceinline__ uint32_t grid_level(const __half2* __restrict__ table, uint32_t size_mask, uint32_t res,
+// NC = true: read-only (ld.global.nc) loads -- query kernel; false: coherent loads -- the training kernel updates the
+// table later in the same launch.
+template <bool NC = true>
+__device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t size_mask, uint32_t res,
                                                float scale, bool dense, float x, float y, float z) {
     float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
     uint32_t g[3];
@@ -105,7 +109,9 @@ __device__ __forceinline__ uint32_t grid_level(const __half2* __restrict__ table
         uint32_t idx;
         if (dense) idx = gl[0] + gl[1] * res + gl[2] * res * res;
         else idx = gl[0] ^ (gl[1] * 2654435761u) ^ (gl[2] * 805459861u);
-        const __half2 v = __ldg(table + (idx & size_mask));
+        __half2 v;
+        if constexpr (NC) v = __ldg(table + (idx & size_mask));
+        else v = table[idx & size_mask];
         acc = __hfma2(__float2half2_rn(w), v, acc);
     }
     return *reinterpret_cast<uint32_t*>(&acc);
@@ -132,6 +138,64 @@ __device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2*
     e[29] = pack_h2(q[11], q[12]);
     e[30] = pack_h2(q[13], q[14]);
     e[31] = 0x3C003C00u;
+}
+
+// ---- Half encoders for the training kernel: two threads share one sample, each produces half of the 16-byte
+// feature chunks (8 features per chunk).  HF = 0: chunks [0, E/16); HF = 1: chunks [E/16, E/8).
+// Frequency (10 chunks): HF0 = tri-wave 36 + one-blob of dim 3 (features 0..39); HF1 = one-blob dims 4..8, albedos, pad.
+template <int HF>
+__device__ __forceinline__ void encode_frequency_half(const float (&q)[15], uint32_t (&e)[20]) {
+    if constexpr (HF == 0) {
+        float t[36];
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+#pragma unroll
+            for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave(q[d], f);
+#pragma unroll
+        for (int i = 0; i < 18; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+        float y[4];
+        oneblob4<true>(q[3], y);
+        e[18] = pack_h2(y[0], y[1]);
+        e[19] = pack_h2(y[2], y[3]);
+    } else {
+#pragma unroll
+        for (int d = 1; d < 6; ++d) {
+            float y[4];
+            oneblob4<true>(q[3 + d], y);
+            e[2 * d - 2] = pack_h2(y[0], y[1]);
+            e[2 * d - 1] = pack_h2(y[2], y[3]);
+        }
+        e[10] = pack_h2(q[9], q[10]);
+        e[11] = pack_h2(q[11], q[12]);
+        e[12] = pack_h2(q[13], q[14]);
+#pragma unroll
+        for (int i = 13; i < 20; ++i) e[i] = 0x3C003C00u;
+    }
+}
+// Hash (8 chunks): HF0 = the 16 grid levels (features 0..31); HF1 = one-blob, albedos, pad (features 32..63).
+template <int HF>
+__device__ __forceinline__ void encode_hash_half(const float (&q)[15], const __half2* grid,
+                                                 const GridMeta& gm, uint32_t (&e)[16]) {
+    if constexpr (HF == 0) {
+#pragma unroll
+        for (int l = 0; l < 16; ++l) {
+            const uint32_t size = gm.offset[l + 1] - gm.offset[l];
+            e[l] = grid_level<false>(grid + gm.offset[l], size - 1, gm.resolution[l], gm.scale[l],
+                                     (gm.dense_mask >> l) & 1, q[0], q[1], q[2]);
+        }
+    } else {
+#pragma unroll
+        for (int d = 0; d < 6; ++d) {
+            float y[4];
+            oneblob4<false>(q[3 + d], y);
+            e[2 * d] = pack_h2(y[0], y[1]);
+            e[2 * d + 1] = pack_h2(y[2], y[3]);
+        }
+        e[12] = pack_h2(q[9], q[10]);
+        e[13] = pack_h2(q[11], q[12]);
+        e[14] = pack_h2(q[13], q[14]);
+        e[15] = 0x3C003C00u;
+    }
 }
 
 }  // namespace nrcb

@@ -12,27 +12,36 @@ struct GridMeta;
 cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
                          int num_sms, cudaStream_t stream);
 
-// nrc_train.cu -- fused forward + loss + backward + per-tile weight-gradient kernel, and the
-// gradient reduction / Adam / EMA kernels.
-struct TrainBuffers {
-    const __half* params;    // fp16 training weights
-    float* partials;         // [n_tiles][n_mlp_params] per-tile weight-gradient partials (loss-scaled)
-    float* grid_grad;        // [n_grid_params] fp32 grid gradient accumulator (Hash), zeroed by the optimizer kernel
-    float* loss_partials;    // [n_tiles]
-};
-cudaError_t launch_train_fwd_bwd(int encoding, const float* in, const float* targets, uint32_t n_local, uint32_t n_global,
-                                 const TrainBuffers& tb, const GridMeta& gm, cudaStream_t stream);
-
-struct OptimState {
-    float* master; __half* params; __half* ema; __half* grads; float* m1; float* m2; uint32_t* steps;
+// nrc_train.cu -- ONE cooperative kernel per optimizer step:
+//   phase 1  per 128-sample tile: encodings, forward, loss, backward, per-tile weight gradients (tcgen05)
+//   phase 2  grid barrier
+//   phase 3  every CTA reduces its slice of the gradient over all tiles (fixed order) and either applies
+//            Adam + EMA to that slice (apply = 1) or leaves the fp32 gradient for a data-parallel all-reduce (apply = 0).
+struct TrainArgs {
+    const float* in; const float* targets;
+    uint32_t n_local, n_global;      // samples of this launch / of the global batch (loss normalisation)
+    // parameter block
+    float* master; __half* params; __half* params_img; __half* ema; __half* grads;
+    float* m1; float* m2; uint32_t* steps;
+    // scratch
+    float* partials;                 // [n_tiles][n_mlp] per-tile weight-gradient partials (loss-scaled)
+    float* grid_grad;                // [n_grid] fp32 scatter accumulator (Hash), cleared in phase 3
+    float* loss_partials;            // [n_tiles]
+    float* grad_f32;                 // [n_params] reduced fp32 gradient (apply = 0: the all-reduce payload)
+    float* loss_out;
+    uint32_t* barrier_counter;       // monotonically increasing arrival counter
+    uint32_t barrier_target;         // value the counter reaches when every CTA of this launch has arrived
     uint32_t n_params, n_mlp;
-    float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
+    float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale, ema_debias_old, ema_debias_new;
+    int apply;
+    long long* timeline;             // optional [n_tiles][8] clock64 stamps of the phases (debug), or nullptr
 };
-// Sums the per-tile partials (+ grid accumulator) into grad_f32[n_params]; writes loss_out = sum(loss_partials).
-cudaError_t launch_reduce_grads(const TrainBuffers& tb, uint32_t n_tiles, uint32_t n_params, uint32_t n_mlp,
-                                float* grad_f32, float* loss_out, cudaStream_t stream);
-// grad_f32 -> fp16 gradient, Adam (adam.h:75-118), EMA (ema.h:62-76); clears grid_grad for the next step.
-cudaError_t launch_adam_ema(const OptimState& os, const float* grad_f32, float* grid_grad_to_clear, uint32_t step,
-                            cudaStream_t stream);
+cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream);
+
+// Adam + EMA from an already reduced fp32 gradient (after a data-parallel all-reduce); clears grid_grad.
+cudaError_t launch_adam_ema(const TrainArgs& a, cudaStream_t stream);
+// Rebuilds the UMMA shared-memory image of the fp16 training weights (after a host upload).
+cudaError_t launch_make_image(const __half* params, __half* params_img, uint32_t enc_width, uint32_t n_mlp,
+                              cudaStream_t stream);
 
 }  // namespace nrcb

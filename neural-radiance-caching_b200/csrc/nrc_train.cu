@@ -1,16 +1,22 @@
-// Fused NRC training step for sm_100a.
-//   kernel 1 (nrc_train_tile_kernel): one CTA per 128-sample tile does what the reference spreads over ~20
-//     launches: encodings, forward MLP with activations kept in shared memory,
-//     RelativeL2Luminance loss + dL/dy (tcnn/losses/relative_l2_luminance.h:54-86), output-ReLU transfer,
-//     the backward chain (tcnn/src/fully_fused_mlp.cu:150-259) and the per-tile weight gradients
-//     dW = dY * X^T (fully_fused_mlp.cu:785,819,828) -- every contraction on tcgen05, accumulators in TMEM.
-//   kernel 2 (nrc_reduce_grads_kernel): deterministic sum of the per-tile partials -> fp32 gradient vector.
-//   kernel 3 (nrc_adam_ema_kernel): fp16 gradient, Adam (tcnn/optimizers/adam.h:75-118), EMA (ema.h:62-76).
+// Fused NRC training step for sm_100a: ONE cooperative kernel per optimizer step.
+//   phase 1 (per 128-sample tile, one CTA each): what the reference spreads over ~20 launches (SURVEY.md K1-K4,
+//     K7-K13): encodings, forward MLP with activations kept in shared memory, RelativeL2Luminance loss + dL/dy
+//     (tcnn/losses/relative_l2_luminance.h:54-86), output-ReLU transfer, the backward chain
+//     (tcnn/src/fully_fused_mlp.cu:150-259) and the per-tile weight gradients dW = dY * X^T
+//     (fully_fused_mlp.cu:785,819,828) -- every contraction on tcgen05, accumulators in TMEM.
+//   phase 2: grid barrier (all CTAs are co-resident: cooperative launch, <= 128 CTAs of 1 per SM).
+//   phase 3: CTA c sums slice c of the per-tile partials in fixed tile order (bit-reproducible) and applies
+//     Adam (tcnn/optimizers/adam.h:75-118) + EMA (ema.h:62-76) to it -- replacing the reference's 6 split-K GEMM
+//     reductions, adam_step, ema_step and the loss reduce_sum (K11, K14-K16).  With apply = 0 the reduced fp32
+//     gradient is left in grad_f32 for a data-parallel all-reduce and nrc_adam_ema_kernel finishes the step.
 //
 // Shared-memory operands use the SWIZZLE_NONE interleaved layout (8x8 fp16 core matrices of 128 B). One image of a
 // [rows x cols] matrix serves both as a K-major operand (K = cols) and, read through an MN-major descriptor,
 // as the transposed operand (K = rows) -- so W is staged once for forward and backward, and each activation /
 // delta tile is written once and consumed by the next layer's MMA and by the weight-gradient MMA.
+// The weight image itself is kept up to date in global memory by the optimizer phase (params_img), so staging is a
+// single bulk copy that overlaps the encode.
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include "nrc_kernels.h"
@@ -19,19 +25,22 @@
 namespace nrcb {
 
 constexpr int kTT = 128;             // samples per tile
-constexpr int kTrainThreads = 160;   // 4 worker warps (one sample per thread) + 1 MMA-issue warp
+constexpr int kWorkerWarps = 8;      // warp w: TMEM lane quadrant w & 3 (rows), column half w >> 2
+constexpr int kTrainThreads = (kWorkerWarps + 1) * 32;   // + 1 MMA-issue warp
 
 template <int E>
 struct TrainSmem {
     static constexpr int kWin = 64 * E * 2, kWhid = 4 * 8192, kWout = 2048;
+    static constexpr int kWbytes = kWin + kWhid + kWout;
     static constexpr int kW = 0;                              // weight images: W_in | W_h1..4 | W_out
-    static constexpr int kX = kW + kWin + kWhid + kWout;      // encoded inputs   [128 x E]
+    static constexpr int kX = kW + kWbytes;                   // encoded inputs   [128 x E]
     static constexpr int kH = kX + 128 * E * 2;               // h1..h5           5 x [128 x 64]
     static constexpr int kDelta = kH + 5 * 16384;             // delta ping-pong  2 x [128 x 64]
     static constexpr int kG = kDelta + 2 * 16384;             // dL/dy            [128 x 16]
     static constexpr int kIn = kG + 4096;                     // raw queries 7680 B
     static constexpr int kBar = kIn + 7680;
     static constexpr int kTotal = kBar + 128;
+    static constexpr int kScratch = kX;                       // phase 3 reuses the activation area
 };
 
 // TMEM columns
@@ -40,14 +49,15 @@ constexpr uint32_t kWgIn = 64;    // dW_in   [64 x E]   (M = 64: row r lives in 
 __host__ __device__ constexpr uint32_t wg_hid_col(int E, int l) { return 64 + E + 64 * l; }  // dW_h(l+1), l = 0..3
 __host__ __device__ constexpr uint32_t wg_out_col(int E) { return 64 + E + 256; }            // dW_out^T [64 x 16]
 
-__device__ __forceinline__ void stage_weight_t(uint8_t* dst, const __half* __restrict__ W, int n_out, int n_in, int tid,
-                                               int nthr) {
-    const int chunks = n_in / 8;
-    for (int i = tid; i < n_out * chunks; i += nthr) {
-        const int o = i / chunks, c = i - o * chunks;
-        const uint4 v = *reinterpret_cast<const uint4*>(W + (size_t)o * n_in + c * 8);
-        *reinterpret_cast<uint4*>(dst + c * (n_out * 16) + (o >> 3) * 128 + (o & 7) * 16) = v;
-    }
+// Position (in halves) of parameter i inside the UMMA weight image: matrix [n_out x n_in] row-major ->
+// (k/8)*(n_out*8) + (o/8)*64 + (o%8)*8 + k%8   (8x8 core matrices of 64 halves).
+__host__ __device__ __forceinline__ uint32_t img_index(uint32_t i, uint32_t E) {
+    uint32_t base, n_out, n_in, r;
+    if (i < 64 * E) { base = 0; n_out = 64; n_in = E; r = i; }
+    else if (i < 64 * E + 4 * 4096) { r = i - 64 * E; base = 64 * E + (r >> 12) * 4096; r &= 4095; n_out = 64; n_in = 64; }
+    else { base = 64 * E + 4 * 4096; r = i - base; n_out = 16; n_in = 64; }
+    const uint32_t o = r / n_in, k = r - o * n_in;
+    return base + (k >> 3) * (n_out * 8) + (o >> 3) * 64 + (o & 7) * 8 + (k & 7);
 }
 
 // row r of a [128 x cols] interleaved image: 16-byte chunk c lives at c*2048 + (r/8)*128 + (r%8)*16
@@ -80,43 +90,71 @@ __device__ __forceinline__ void mma_wgrad(uint32_t d, uint32_t delta_img, uint32
         umma_ss(d, umma_desc(delta_img + k * 256, 128, 2048), umma_desc(act_img + k * 256, 128, 2048), idesc, k > 0);
 }
 
+// ---------------------------------------------------------------- optimizer (per parameter)
+// adam_step (tcnn/optimizers/adam.h:75-118) followed by ema_step_half_precision (ema.h:62-76).  `g32` is the
+// reduced fp32 gradient (loss-scaled); the reference's gradient buffer is fp16 (trainer.h:322-336), so it is
+// rounded to fp16 first.  Also maintains the UMMA image of the fp16 training weights.
+__device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E) {
+    const __half gh = __float2half_rn(g32);
+    a.grads[i] = gh;
+    float gradient = __half2float(gh) / a.loss_scale;
+    const bool is_matrix = i < a.n_mlp;
+    __half w_half = a.params[i];
+    if (is_matrix || gradient != 0.0f) {   // grid parameters without gradient are skipped entirely (adam.h:80-82)
+        const float weight_fp = a.master[i];
+        if (is_matrix) gradient += a.l2_reg * weight_fp;
+        const float gradient_sq = gradient * gradient;
+        const float m1 = a.m1[i] = a.beta1 * a.m1[i] + (1.0f - a.beta1) * gradient;
+        const float m2 = a.m2[i] = a.beta2 * a.m2[i] + (1.0f - a.beta2) * gradient_sq;
+        const uint32_t cur = ++a.steps[i];
+        const float lr = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+        const float eff = fminf(fmaxf(lr / (sqrtf(m2) + a.eps), 0.0f), 3.402823466e+38f);
+        const float new_weight = weight_fp - eff * m1;
+        a.master[i] = new_weight;
+        w_half = __float2half_rn(new_weight);
+        a.params[i] = w_half;
+        if (is_matrix) a.params_img[img_index(i, E)] = w_half;
+    }
+    const float filtered = (__half2float(a.ema[i]) * a.ema_decay * a.ema_debias_old +
+                            __half2float(w_half) * (1.0f - a.ema_decay)) * a.ema_debias_new;
+    a.ema[i] = __float2half_rn(filtered);
+}
+
+// ---------------------------------------------------------------- the step kernel
 template <int ENC>
 __global__ void __launch_bounds__(kTrainThreads, 1)
-nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ targets, uint32_t n_global,
-                      const __half* __restrict__ params, float* __restrict__ partials, float* __restrict__ grid_grad,
-                      float* __restrict__ loss_partials, GridMeta gm) {
+nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     constexpr int E = ENC == 0 ? 80 : 64;
     constexpr int NMLP = 64 * E + 4 * 4096 + 1024;
+    constexpr int CH = E / 16;   // 16-byte feature chunks per encode half
     using L = TrainSmem<E>;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBar);
-    uint64_t* a_ready = bars;       // workers -> issuer (count 4)
+    uint64_t* a_ready = bars;       // workers -> issuer (count kWorkerWarps)
     uint64_t* d_ready = bars + 1;   // issuer  -> workers
     uint64_t* in_full = bars + 2;   // bulk copy of the raw queries
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
-    float* warp_loss = reinterpret_cast<float*>(bars + 4);
+    uint64_t* w_full = bars + 3;    // bulk copy of the weight image
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+    float* warp_loss = reinterpret_cast<float*>(bars + 5);   // [4]
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t tile = blockIdx.x;
+    const uint32_t n_tiles = gridDim.x;
+    const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0;
+    auto stamp = [&](int slot) { if (a.timeline && tid == 0) a.timeline[tile * 8 + slot] = clock64(); };
+    stamp(0);
 
-    {
-        const __half* W = params;
-        stage_weight_t(smem + L::kW, W, 64, E, tid, kTrainThreads);
-        W += 64 * E;
-        for (int l = 0; l < 4; ++l, W += 4096) stage_weight_t(smem + L::kW + L::kWin + l * 8192, W, 64, 64, tid, kTrainThreads);
-        stage_weight_t(smem + L::kW + L::kWin + L::kWhid, W, 16, 64, tid, kTrainThreads);
-    }
     if (tid == 0) {
-        mbar_init(a_ready, 4); mbar_init(d_ready, 1); mbar_init(in_full, 1);
+        mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1);
         fence_mbar_init();
-        const float* src = in + (size_t)tile * kTT * 15;
-        if ((reinterpret_cast<uintptr_t>(in) & 15) == 0) {
+        mbar_arrive_expect_tx(w_full, L::kWbytes);
+        bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
+        if (in_aligned) {
             mbar_arrive_expect_tx(in_full, 7680);
-            bulk_g2s(smem + L::kIn, src, 7680, in_full);
+            bulk_g2s(smem + L::kIn, a.in + (size_t)tile * kTT * 15, 7680, in_full);
         }
     }
-    if (warp == 4) tmem_alloc(tmem_slot, 512);
-    fence_proxy_async_smem();
+    if (warp == kWorkerWarps) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -124,12 +162,13 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
     const uint32_t sW = smem_u32(smem + L::kW), sX = smem_u32(smem + L::kX), sH = smem_u32(smem + L::kH);
     const uint32_t sDl = smem_u32(smem + L::kDelta), sG = smem_u32(smem + L::kG);
 
-    if (warp == 4) {
+    if (warp == kWorkerWarps) {
         // ======================= MMA issuer =======================
         const bool leader = elect_one();
         uint32_t ph = 0;
         auto wait_workers = [&]() { mbar_wait_uniform(a_ready, ph); ph ^= 1; tc_fence_after(); };
         const uint32_t acc = tmem_base + kAcc;
+        mbar_wait(w_full, 0);              // weight image landed (async proxy write -> async proxy read)
         // forward
         wait_workers();
         if (leader) { mma_fwd(acc, sX, sW, 64, E / 16); umma_commit(d_ready); }
@@ -170,63 +209,70 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
         }
         __syncwarp();
     } else {
-        // ======================= workers: thread = sample =======================
-        const uint32_t row = warp * 32 + lane;
-        const uint32_t tq = tmem_base + ((warp * 32u) << 16);
-        const uint32_t n_total = n_global * 3;
+        // ======================= workers: two threads per sample (column halves) =======================
+        const int qd = warp & 3, hf = warp >> 2;
+        const uint32_t row = qd * 32 + lane;
+        const uint32_t tq = tmem_base + ((qd * 32u) << 16);
+        const uint32_t cb = hf * 32;          // this thread's 32 accumulator columns
+        const uint32_t n_total = a.n_global * 3;
         uint32_t ph = 0;
         auto wait_mma = [&]() { mbar_wait(d_ready, ph); ph ^= 1; tc_fence_after(); };
         auto signal = [&]() { fence_proxy_async_smem(); tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(a_ready); };
 
         float q[15];
-        if ((reinterpret_cast<uintptr_t>(in) & 15) == 0) {
+        if (in_aligned) {
             mbar_wait(in_full, 0);
             const float* s_in = reinterpret_cast<const float*>(smem + L::kIn);
 #pragma unroll
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
         } else {
 #pragma unroll
-            for (int i = 0; i < 15; ++i) q[i] = __ldg(in + ((size_t)tile * kTT + row) * 15 + i);
+            for (int i = 0; i < 15; ++i) q[i] = __ldg(a.in + ((size_t)tile * kTT + row) * 15 + i);
         }
-        float tg[3];
+        float tg[3] = {0.0f, 0.0f, 0.0f};
+        if (hf == 0) {
 #pragma unroll
-        for (int c = 0; c < 3; ++c) tg[c] = __ldg(targets + ((size_t)tile * kTT + row) * 3 + c);
+            for (int c = 0; c < 3; ++c) tg[c] = __ldg(a.targets + ((size_t)tile * kTT + row) * 3 + c);
+        }
         {
-            uint32_t e[E / 2];
-            if constexpr (ENC == 0) encode_frequency(q, e);
-            else encode_hash(q, reinterpret_cast<const __half2*>(params + NMLP), gm, e);
+            uint32_t e[E / 4];
+            if constexpr (ENC == 0) {
+                if (hf == 0) encode_frequency_half<0>(q, e); else encode_frequency_half<1>(q, e);
+            } else {
+                const __half2* grid = reinterpret_cast<const __half2*>(a.params + NMLP);
+                if (hf == 0) encode_hash_half<0>(q, grid, gm, e); else encode_hash_half<1>(q, grid, gm, e);
+            }
 #pragma unroll
-            for (int c = 0; c < E / 8; ++c)
-                *reinterpret_cast<uint4*>(row_chunk(smem + L::kX, row, c)) = make_uint4(e[4 * c], e[4 * c + 1], e[4 * c + 2], e[4 * c + 3]);
+            for (int c = 0; c < CH; ++c)
+                *reinterpret_cast<uint4*>(row_chunk(smem + L::kX, row, hf * CH + c)) = make_uint4(e[4 * c], e[4 * c + 1], e[4 * c + 2], e[4 * c + 3]);
         }
         signal();
-        // forward: h_(l+1) = relu(acc) -> fp16 -> smem; keep the relu mask (2 x 32 bits per layer) in registers
-        uint32_t mask[5][2];
+        stamp(1);
+        // forward: h_(l+1) = relu(acc) -> fp16 -> smem; keep the relu mask of this thread's 32 columns in a register
+        uint32_t mask[5];
 #pragma unroll
         for (int l = 0; l < 5; ++l) {
             wait_mma();
+            uint32_t v[32];
+            tmem_ld32(tq + kAcc + cb, v);
+            tmem_wait_ld();
+            uint32_t m = 0, w[16];
 #pragma unroll
-            for (int hc = 0; hc < 2; ++hc) {
-                uint32_t v[32];
-                tmem_ld32(tq + kAcc + hc * 32, v);
-                tmem_wait_ld();
-                uint32_t m = 0, w[16];
+            for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > 0.0f ? 1u : 0u) << i;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > 0.0f ? 1u : 0u) << i;
+            for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+            mask[l] = m;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-                mask[l][hc] = m;
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    *reinterpret_cast<uint4*>(row_chunk(smem + L::kH + l * 16384, row, hc * 4 + c)) =
-                        make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
-            }
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<uint4*>(row_chunk(smem + L::kH + l * 16384, row, hf * 4 + c)) =
+                    make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
             signal();
         }
         // output + loss (relative_l2_luminance.h:62-86) + output-ReLU transfer (common_device.h:241-249)
         wait_mma();
-        float loss = 0.0f;
-        {
+        stamp(2);
+        if (hf == 0) {
+            float loss = 0.0f;
             uint32_t v[16];
             tmem_ld16(tq + kAcc, v);
             tmem_wait_ld();
@@ -244,43 +290,42 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
             }
             *reinterpret_cast<uint4*>(row_chunk(smem + L::kG, row, 0)) = make_uint4(pack_h2(gr[0], gr[1]), pack_h2(gr[2], 0.0f), 0u, 0u);
             *reinterpret_cast<uint4*>(row_chunk(smem + L::kG, row, 1)) = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
+            if (lane == 0) warp_loss[qd] = loss;
         }
         signal();
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) loss += __shfl_xor_sync(0xffffffffu, loss, o);
-        if (lane == 0) warp_loss[warp] = loss;
         // backward chain: delta_l = (W^T delta_(l+1)) .* [h_l > 0], rounded to fp16
 #pragma unroll
         for (int l = 4; l >= 0; --l) {
             wait_mma();
             uint8_t* dbuf = smem + L::kDelta + ((4 - l) & 1) * 16384;
+            uint32_t v[32], w[16];
+            tmem_ld32(tq + kAcc + cb, v);
+            tmem_wait_ld();
+            const uint32_t m = mask[l];
 #pragma unroll
-            for (int hc = 0; hc < 2; ++hc) {
-                uint32_t v[32], w[16];
-                tmem_ld32(tq + kAcc + hc * 32, v);
-                tmem_wait_ld();
-                const uint32_t m = mask[l][hc];
+            for (int i = 0; i < 16; ++i)
+                w[i] = pack_h2((m >> (2 * i)) & 1 ? __uint_as_float(v[2 * i]) : 0.0f,
+                               (m >> (2 * i + 1)) & 1 ? __uint_as_float(v[2 * i + 1]) : 0.0f);
 #pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    w[i] = pack_h2((m >> (2 * i)) & 1 ? __uint_as_float(v[2 * i]) : 0.0f,
-                                   (m >> (2 * i + 1)) & 1 ? __uint_as_float(v[2 * i + 1]) : 0.0f);
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    *reinterpret_cast<uint4*>(row_chunk(dbuf, row, hc * 4 + c)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
-            }
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<uint4*>(row_chunk(dbuf, row, hf * 4 + c)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
             signal();
         }
         // all MMAs done: weight-gradient accumulators (and, Hash, dL/d(grid features)) are in TMEM
         wait_mma();
-        if (warp == 0 && lane == 0) loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
-        if constexpr (ENC == 1) {
-            uint32_t v[32];
-            tmem_ld32(tq + kAcc, v);
+        stamp(3);
+        if (warp == 0 && lane == 0) a.loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
+        if constexpr (ENC == 1) {   // grid gradient scatter: half hf handles levels 8*hf .. 8*hf+7 (columns 16*hf ..)
+            uint32_t v[16];
+            tmem_ld16(tq + kAcc + hf * 16, v);
             tmem_wait_ld();
 #pragma unroll 1
-            for (int lv = 0; lv < 16; ++lv) {
-                const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv])));
-                const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv + 1])));
+            for (int j = 0; j < 8; ++j) {
+                const int lv = hf * 8 + j;
+                const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * j])));
+                const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * j + 1])));
                 if (g0 == 0.0f && g1 == 0.0f) continue;
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], res = gm.resolution[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
@@ -293,7 +338,7 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
                     gp[d] = (uint32_t)(int)fl;
                     p[d] -= fl;
                 }
-                float* gl = grid_grad + (size_t)gm.offset[lv] * 2;
+                float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     float wgt = 1.0f;
@@ -311,27 +356,31 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
         }
         // per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.
         // The TMEM loads are warp-wide (.sync.aligned): every lane executes them, lanes 0..15 store.
+        // Column chunks of 16 are split between the two halves.
         {
             const bool owner = lane < 16;
-            const uint32_t o = warp * 16 + (lane & 15);
-            float* P = partials + (size_t)tile * NMLP;
-            auto dump = [&](uint32_t col, float* dst, int ncols) {   // dst: row o of a row-major [64 x ncols] block
-                for (int c0 = 0; c0 < ncols; c0 += 16) {
-                    uint32_t v[16];
-                    tmem_ld16(tq + col + c0, v);
-                    tmem_wait_ld();
-                    if (owner) {
+            const uint32_t o = qd * 16 + (lane & 15);
+            float* P = a.partials + (size_t)tile * NMLP;
+            auto dump16 = [&](uint32_t col, float* dst) {   // 16 consecutive floats of row o
+                uint32_t v[16];
+                tmem_ld16(tq + col, v);
+                tmem_wait_ld();
+                if (owner) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            reinterpret_cast<float4*>(dst + c0)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
-                                                                                 __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-                    }
+                    for (int i = 0; i < 4; ++i)
+                        reinterpret_cast<float4*>(dst)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                                        __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
                 }
             };
-            dump(kWgIn, P + o * E, E);
+            constexpr int kInChunks = E / 16;                 // 5 (Frequency) / 4 (Hash)
+            constexpr int kSplit = (kInChunks + 1) / 2;       // half 0: chunks [0, kSplit); half 1: the rest
+            for (int c = (hf == 0 ? 0 : kSplit); c < (hf == 0 ? kSplit : kInChunks); ++c) dump16(kWgIn + c * 16, P + o * E + c * 16);
 #pragma unroll
-            for (int l = 0; l < 4; ++l) dump(wg_hid_col(E, l), P + 64 * E + l * 4096 + o * 64, 64);
-            {   // dW_out^T [64 x 16]: element (k = o, c) -> dW_out[c][k]
+            for (int l = 0; l < 4; ++l)
+#pragma unroll
+                for (int c = 0; c < 2; ++c)
+                    dump16(wg_hid_col(E, l) + (hf * 2 + c) * 16, P + 64 * E + l * 4096 + o * 64 + (hf * 2 + c) * 16);
+            if (hf == 1) {   // dW_out^T [64 x 16]: element (k = o, c) -> dW_out[c][k]
                 uint32_t v[16];
                 tmem_ld16(tq + wg_out_col(E), v);
                 tmem_wait_ld();
@@ -342,106 +391,120 @@ nrc_train_tile_kernel(const float* __restrict__ in, const float* __restrict__ ta
             }
         }
     }
+    // ---- phase 2: publish this tile's partials, free TMEM, wait for every tile of the batch
+    stamp(4);
+    __threadfence();
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem_base, 512);
-}
-
-// ---------------------------------------------------------------- gradient reduction
-// grad[i] = sum over tiles of partials[t][i] (fixed order -> bit-reproducible), grid part copied from the
-// fp32 scatter accumulator; block 0 also reduces the per-tile losses (Trainer::loss, trainer.h:205-207).
-__global__ void __launch_bounds__(256)
-nrc_reduce_grads_kernel(const float* __restrict__ partials, const float* __restrict__ grid_grad,
-                        const float* __restrict__ loss_partials, uint32_t n_tiles, uint32_t n_params, uint32_t n_mlp,
-                        float* __restrict__ grad, float* __restrict__ loss_out) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n_mlp) {
-        float a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        uint32_t t = 0;
-        for (; t + 4 <= n_tiles; t += 4) {
-            a0 += partials[(size_t)(t + 0) * n_mlp + i];
-            a1 += partials[(size_t)(t + 1) * n_mlp + i];
-            a2 += partials[(size_t)(t + 2) * n_mlp + i];
-            a3 += partials[(size_t)(t + 3) * n_mlp + i];
-        }
-        for (; t < n_tiles; ++t) a0 += partials[(size_t)t * n_mlp + i];
-        grad[i] = (a0 + a1) + (a2 + a3);
-    } else if (i < n_params) {
-        grad[i] = grid_grad[i - n_mlp];
+    if (warp == kWorkerWarps) tmem_dealloc(tmem_base, 512);
+    if (tid == 0) {
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
+        uint32_t seen, spins = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
+            if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+        } while ((int32_t)(seen - a.barrier_target) < 0);
     }
-    if (blockIdx.x == 0 && threadIdx.x < 32) {
-        float l = 0;
-        for (uint32_t t = threadIdx.x; t < n_tiles; t += 32) l += loss_partials[t];
+    __syncthreads();
+    stamp(5);
+
+    // ---- phase 3: slice c of the gradient: fixed-order sum over tiles, then Adam + EMA (or store for all-reduce)
+    {
+        const uint32_t S = ((NMLP + n_tiles - 1) / n_tiles + 3) & ~3u;     // parameters per CTA (multiple of 4)
+        const uint32_t lo = min((uint32_t)NMLP, tile * S), hi = min((uint32_t)NMLP, lo + S);
+        const uint32_t ncol4 = (hi - lo) >> 2;                             // NMLP % 4 == 0 -> whole float4 columns
+        float4* scratch = reinterpret_cast<float4*>(smem + L::kScratch);   // [groups][ncol4]
+        const uint32_t groups = ncol4 == 0 ? 0 : (ncol4 >= (uint32_t)kTrainThreads ? 1 : min((uint32_t)kTrainThreads / ncol4, n_tiles));
+        for (uint32_t w = tid; w < groups * ncol4; w += kTrainThreads) {   // one pass when the batch has >= 20 tiles
+            const uint32_t g = w / ncol4, c4 = w - g * ncol4;
+            const float* src = a.partials + lo + 4 * c4;
+            float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            // batches of 8 independent L2 loads in flight (a dependent chain of ~0.4 us L2 hits otherwise), summed in
+            // increasing tile order
+            for (uint32_t t0 = g; t0 < n_tiles; t0 += 8 * groups) {
+                float4 v[8];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-        if (threadIdx.x == 0) *loss_out = l;
+                for (int u = 0; u < 8; ++u) {
+                    const uint32_t t = t0 + u * groups;
+                    v[u] = t < n_tiles ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)t * NMLP)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+            }
+            scratch[w] = acc;
+        }
+        __syncthreads();
+        for (uint32_t j = tid; j < hi - lo; j += kTrainThreads) {
+            const float* sc = reinterpret_cast<const float*>(scratch);
+            float gsum = 0.0f;
+            for (uint32_t g = 0; g < groups; ++g) gsum += sc[(g * ncol4 + (j >> 2)) * 4 + (j & 3)];
+            a.grad_f32[lo + j] = gsum;
+            if (a.apply) adam_ema_param(a, lo + j, gsum, E);
+        }
+        if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
+            const uint32_t n_grid = a.n_params - NMLP;
+            const uint32_t SG = (n_grid + n_tiles - 1) / n_tiles;
+            const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
+            for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
+                const float g = __ldcg(a.grid_grad + j);
+                a.grad_f32[NMLP + j] = g;
+                if (a.apply) { adam_ema_param(a, NMLP + j, g, E); a.grid_grad[j] = 0.0f; }
+            }
+        }
+        if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
+            float l = 0.0f;
+            for (uint32_t t = lane; t < n_tiles; t += 32) l += __ldcg(a.loss_partials + t);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+            if (lane == 0) *a.loss_out = l;
+        }
     }
+    __syncthreads();
+    stamp(6);
 }
 
-// ---------------------------------------------------------------- optimizer
-// adam_step (tcnn/optimizers/adam.h:75-118) followed by ema_step_half_precision (ema.h:62-76) per parameter.
+// ---------------------------------------------------------------- stand-alone optimizer (data-parallel path)
+// After the all-reduce of grad_f32: the same per-parameter update on every rank; clears the grid accumulator.
 __global__ void __launch_bounds__(256)
-nrc_adam_ema_kernel(OptimState os, const float* __restrict__ grad_f32, float* __restrict__ grid_grad_to_clear,
-                    float ema_debias_old, float ema_debias_new) {
+nrc_adam_ema_kernel(const TrainArgs a, uint32_t E) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= os.n_params) return;
-    const __half gh = __float2half_rn(grad_f32[i]);   // the reference's gradient buffer is fp16 (trainer.h:322-336)
-    os.grads[i] = gh;
-    float gradient = __half2float(gh) / os.loss_scale;
-    const bool is_matrix = i < os.n_mlp;
-    if (!is_matrix) grid_grad_to_clear[i - os.n_mlp] = 0.0f;
-    __half w_half = os.params[i];
-    if (is_matrix || gradient != 0.0f) {
-        const float weight_fp = os.master[i];
-        if (is_matrix) gradient += os.l2_reg * weight_fp;
-        const float gradient_sq = gradient * gradient;
-        const float m1 = os.m1[i] = os.beta1 * os.m1[i] + (1.0f - os.beta1) * gradient;
-        const float m2 = os.m2[i] = os.beta2 * os.m2[i] + (1.0f - os.beta2) * gradient_sq;
-        const uint32_t cur = ++os.steps[i];
-        const float lr = os.lr * (sqrtf(1.0f - powf(os.beta2, (float)cur)) / (1.0f - powf(os.beta1, (float)cur)));
-        const float eff = fminf(fmaxf(lr / (sqrtf(m2) + os.eps), 0.0f), 3.402823466e+38f);
-        const float new_weight = weight_fp - eff * m1;
-        os.master[i] = new_weight;
-        w_half = __float2half_rn(new_weight);
-        os.params[i] = w_half;
-    }
-    const float filtered = (__half2float(os.ema[i]) * os.ema_decay * ema_debias_old +
-                            __half2float(w_half) * (1.0f - os.ema_decay)) * ema_debias_new;
-    os.ema[i] = __float2half_rn(filtered);
+    if (i >= a.n_params) return;
+    adam_ema_param(a, i, a.grad_f32[i], E);
+    if (i >= a.n_mlp) a.grid_grad[i - a.n_mlp] = 0.0f;
+}
+
+__global__ void __launch_bounds__(256)
+nrc_make_image_kernel(const __half* __restrict__ params, __half* __restrict__ img, uint32_t E, uint32_t n_mlp) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_mlp) img[img_index(i, E)] = params[i];
 }
 
 // ---------------------------------------------------------------- launchers
 template <int ENC>
-static cudaError_t launch_train_t(const float* in, const float* targets, uint32_t n_local, uint32_t n_global,
-                                  const TrainBuffers& tb, const GridMeta& gm, cudaStream_t stream) {
+static cudaError_t launch_train_t(const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
     using L = TrainSmem<ENC == 0 ? 80 : 64>;
     static bool configured[2] = {false, false};
     if (!configured[ENC]) {
-        cudaError_t e = cudaFuncSetAttribute(nrc_train_tile_kernel<ENC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+        cudaError_t e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
         if (e != cudaSuccess) return e;
         configured[ENC] = true;
     }
-    nrc_train_tile_kernel<ENC><<<n_local / kTT, kTrainThreads, L::kTotal, stream>>>(in, targets, n_global, tb.params, tb.partials,
-                                                                                  tb.grid_grad, tb.loss_partials, gm);
+    // Cooperative launch: the grid barrier needs every CTA resident (<= 128 CTAs, one per SM).
+    void* args[2] = {const_cast<TrainArgs*>(&a), const_cast<GridMeta*>(&gm)};
+    return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC>), dim3(a.n_local / kTT),
+                                       dim3(kTrainThreads), args, L::kTotal, stream);
+}
+cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
+    return encoding == 0 ? launch_train_t<0>(a, gm, stream) : launch_train_t<1>(a, gm, stream);
+}
+cudaError_t launch_adam_ema(const TrainArgs& a, cudaStream_t stream) {
+    const uint32_t E = a.n_mlp == 64 * 80 + 4 * 4096 + 1024 ? 80 : 64;
+    nrc_adam_ema_kernel<<<(a.n_params + 255) / 256, 256, 0, stream>>>(a, E);
     return cudaGetLastError();
 }
-cudaError_t launch_train_fwd_bwd(int encoding, const float* in, const float* targets, uint32_t n_local, uint32_t n_global,
-                                 const TrainBuffers& tb, const GridMeta& gm, cudaStream_t stream) {
-    return encoding == 0 ? launch_train_t<0>(in, targets, n_local, n_global, tb, gm, stream)
-                         : launch_train_t<1>(in, targets, n_local, n_global, tb, gm, stream);
-}
-cudaError_t launch_reduce_grads(const TrainBuffers& tb, uint32_t n_tiles, uint32_t n_params, uint32_t n_mlp, float* grad_f32,
-                                float* loss_out, cudaStream_t stream) {
-    nrc_reduce_grads_kernel<<<(n_params + 255) / 256, 256, 0, stream>>>(tb.partials, tb.grid_grad, tb.loss_partials, n_tiles,
-                                                                        n_params, n_mlp, grad_f32, loss_out);
-    return cudaGetLastError();
-}
-cudaError_t launch_adam_ema(const OptimState& os, const float* grad_f32, float* grid_grad_to_clear, uint32_t step,
-                            cudaStream_t stream) {
-    // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double
-    const float debias_old = 1.0f - (float)pow((double)os.ema_decay, (double)(step - 1));
-    const float debias_new = 1.0f / (1.0f - (float)pow((double)os.ema_decay, (double)step));
-    nrc_adam_ema_kernel<<<(os.n_params + 255) / 256, 256, 0, stream>>>(os, grad_f32, grid_grad_to_clear, debias_old, debias_new);
+cudaError_t launch_make_image(const __half* params, __half* params_img, uint32_t enc_width, uint32_t n_mlp,
+                              cudaStream_t stream) {
+    nrc_make_image_kernel<<<(n_mlp + 255) / 256, 256, 0, stream>>>(params, params_img, enc_width, n_mlp);
     return cudaGetLastError();
 }
 

@@ -1,0 +1,27 @@
+"""Prints the phase timeline (clock64 deltas, median over tiles) of the fused training step kernel."""
+import os, sys
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import __graft_entry__ as entry
+pkg = entry.load_package(); synth = entry.load_package_synthetic()
+for enc in (0, 1):
+    net = pkg.Network(); net.init(0, enc)
+    q = synth.cornell_queries(16384, seed=1); t = synth.radiance_targets(q, seed=1)
+    qd, td = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+    for _ in range(5): net.train(qd, td)
+    net.debug_train_timeline(True)
+    for _ in range(3): net.train(qd, td)
+    tl = net.debug_train_timeline(True, read=True).astype(np.float64)
+    d = np.diff(tl[:, :7], axis=1) / 1.965e3   # us at 1965 MHz
+    names = ["setup+encode", "forward", "backward+wgrad", "scatter+dump", "grid barrier", "reduce+adam"]
+    print("enc", enc, " ".join(f"{n}={np.median(d[:, i]):.2f}us(max {d[:, i].max():.2f})" for i, n in enumerate(names)),
+          f"total={np.median(tl[:, 6] - tl[:, 0]) / 1.965e3:.2f}us")
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    net.debug_train_timeline(False)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(200): net.train(qd, td)
+    e1.record(); torch.cuda.synchronize()
+    print("   back-to-back step:", e0.elapsed_time(e1) / 200 * 1e3, "us")
+    net.destroy()
