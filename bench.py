@@ -48,6 +48,8 @@ def parse_args():
     ap.add_argument("--queries", type=int, default=FRAME_QUERIES, help="queries per update per GPU")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dp", choices=["fused", "nccl"], default="fused",
+                    help="multi-GPU gradient all-reduce: fused into the step kernel over NVLink peer memory, or NCCL")
     ap.add_argument("--ref-gpu", action="store_true",
                     help="also time the reference's own tcnn build (oracle/_ref/libnrc_ref.so) on this GPU")
     return ap.parse_args()
@@ -145,7 +147,7 @@ def cpu_update_rate(orc, synth, enc, nq, threads, seconds_budget=20.0):
     return (nq + n_train) / t_update, t_update, sample
 
 
-def run_reference(args, enc):
+def run_reference(args, enc, out):
     """--impl reference: the reference has no CPU implementation of this path (every function is __global__);
     the timed code is oracle/'s scalar C restatement (kind "port") on all host threads.  Each step is a bounded
     sample of the update."""
@@ -191,7 +193,7 @@ def run_reference(args, enc):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    print(json.dumps(line), file=out, flush=True)
 
 
 class DevPtr:
@@ -232,7 +234,7 @@ def run_ours(args, enc):
     net = pkg.Network()
     net.init(sp, enc)
 
-    dp = importlib.import_module("nrc_b200.dist").DataParallelTrainer(net) if world > 1 else None
+    dp = importlib.import_module("nrc_b200.dist").DataParallelTrainer(net, mode=args.dp) if world > 1 else None
 
     def train_batch(b, want_loss=False):
         qs = q_ptr_t + b * BATCH_SIZE * 60
@@ -335,7 +337,7 @@ def run_ours(args, enc):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16",
             "data": "synthetic",
             "config": {"workload": workload_name(enc, nq), "queries_per_gpu": nq, "train_samples_per_gpu": n_train,
-                       "parallelism": f"dp{world}" if world > 1 else "single",
+                       "parallelism": (f"dp{world} ({args.dp} all-reduce)") if world > 1 else "single",
                        "l2": f"inputs larger than L2 ({nq * 60 / 1e6:.0f} MB of queries per step vs 126 MB L2)"},
             "queries_per_s": world * nq / (t_inf_ms * 1e-3),
             "train_samples_per_s": world * n_train / max((ms_step - t_inf_ms) * 1e-3, 1e-9),
@@ -362,10 +364,19 @@ TRAFFIC_BYTES = {}   # (encoding, queries) -> dram bytes per launch from an `ncu
 
 
 def main():
+    # Libraries (NCCL version banner ...) write to fd 1; the contract is ONE JSON line on stdout, so fd 1 is pointed at
+    # stderr for the duration of the run and the result goes to the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    _main(real_stdout)
+
+
+def _main(out):
     args = parse_args()
     enc = 0 if args.encoding == "frequency" else 1
     if args.impl == "reference":
-        run_reference(args, enc)
+        run_reference(args, enc, out)
         return
     line, rank, world = run_ours(args, enc)
     if rank == 0:
@@ -378,7 +389,7 @@ def main():
                                     "ms_per_update": t_update * 1e3}
         if args.ref_gpu and world == 1:
             line["reference_gpu"] = time_reference_gpu(enc, args.queries)
-        print(json.dumps(line))
+        print(json.dumps(line), file=out, flush=True)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()

@@ -81,6 +81,17 @@ int nrc_b200_train_grad(nrc_b200_handle h, const float* queries_d, const float* 
                         uint32_t n_global, float** grad_d, void* cu_stream);
 int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h);
 
+/* Data-parallel training with the gradient all-reduce FUSED into the step kernel (peer stores + flags over NVLink;
+ * one process per GPU, CUDA IPC).  Protocol: every rank calls nrc_b200_dp_export, the host all-gathers the
+ * NRC_B200_IPC_HANDLE_BYTES-byte handles (any transport), every rank calls nrc_b200_dp_connect with the gathered
+ * array, synchronises with its peers once (barrier), and from then on calls nrc_b200_train_dp once per step on
+ * every rank.  Replicas must start from identical weights.  World size <= 8 (one NVSwitch domain). */
+#define NRC_B200_IPC_HANDLE_BYTES 64
+int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out);
+int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_handles);
+int nrc_b200_train_dp(nrc_b200_handle h, const float* queries_d, const float* targets_d, uint32_t n_local,
+                      uint32_t n_global, void* cu_stream, float* loss_h);
+
 /* Parity-harness access to the parameters (Trainer::params() / set_params(), trainer.h:226-269). */
 typedef enum nrc_b200_param_kind {
     NRC_B200_PARAMS_MASTER_F32 = 0,  /* fp32 master weights  */

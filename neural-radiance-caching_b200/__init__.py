@@ -31,7 +31,7 @@ ABI_SYMBOLS = [
     "nrc_b200_train", "nrc_b200_set_stream", "nrc_b200_set_learning_rate", "nrc_b200_get_learning_rate",
     "nrc_b200_infer_host", "nrc_b200_train_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
     "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
-    "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline",
+    "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline", "nrc_b200_dp_export", "nrc_b200_dp_connect", "nrc_b200_train_dp",
 ]
 
 
@@ -78,6 +78,9 @@ def lib():
         L.nrc_b200_last_error.restype = ctypes.c_char_p
         L.nrc_b200_launch_count.argtypes = [vp, P(u64)]
         L.nrc_b200_debug_train_timeline.argtypes = [vp, i32, vp]
+        L.nrc_b200_dp_export.argtypes = [vp, vp]
+        L.nrc_b200_dp_connect.argtypes = [vp, i32, i32, vp]
+        L.nrc_b200_train_dp.argtypes = [vp, vp, vp, u32, u32, vp, P(f32)]
         _lib = L
     return _lib
 
@@ -179,6 +182,23 @@ class Network:
     def train_apply(self, stream=None, want_loss=False):
         loss = ctypes.c_float()
         _check(lib().nrc_b200_train_apply(self._h, _ptr(stream), ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
+
+    def dp_export(self):
+        """64-byte CUDA IPC handle of this rank's exchange buffer (bytes)."""
+        buf = ctypes.create_string_buffer(64)
+        _check(lib().nrc_b200_dp_export(self._h, buf))
+        return buf.raw
+
+    def dp_connect(self, rank, world, handles):
+        """handles: bytes, world x 64, in rank order (all-gathered by the caller)."""
+        assert len(handles) == 64 * world
+        _check(lib().nrc_b200_dp_connect(self._h, int(rank), int(world), ctypes.c_char_p(handles)))
+
+    def train_dp(self, inputs_d, targets_d, n_local, n_global, stream=None, want_loss=False):
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train_dp(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global), _ptr(stream),
+                                       ctypes.byref(loss) if want_loss else None))
         return loss.value if want_loss else None
 
     def last_loss_device(self):

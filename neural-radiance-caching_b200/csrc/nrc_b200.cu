@@ -35,7 +35,10 @@ struct nrc_b200_network {
     float* master = nullptr; __half* params = nullptr; __half* ema = nullptr; __half* grads = nullptr;
     __half* params_img = nullptr;   // UMMA shared-memory image of the fp16 training MLP weights (bulk-copied by the step kernel)
     uint32_t* barrier_counter = nullptr; uint32_t barrier_total = 0;
-    long long* timeline = nullptr;   // debug: per-tile phase stamps of the step kernel   // grid barrier of the cooperative step kernel
+    long long* timeline = nullptr;   // debug: per-tile phase stamps of the step kernel
+    // data-parallel exchange over NVLink peer memory (nrc_b200_dp_*): one IPC allocation [xbuf | xflag] per rank
+    void* dp_local = nullptr; void* dp_peer[kMaxDpRanks] = {}; int dp_rank = 0, dp_world = 1;
+    uint32_t x_stride = 0; size_t xbuf_bytes = 0;   // grid barrier of the cooperative step kernel
     float* m1 = nullptr; float* m2 = nullptr; uint32_t* steps = nullptr;
     // training scratch (device)
     float* partials = nullptr; float* grid_grad = nullptr; float* loss_partials = nullptr;
@@ -93,11 +96,21 @@ static uint64_t splitmix64(uint64_t& s) {
 }
 static float u01(uint64_t& s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16777216.0f); }
 
+static void dp_teardown(Net* n) {
+    for (int r = 0; r < kMaxDpRanks; ++r) {
+        if (n->dp_peer[r] && r != n->dp_rank) cudaIpcCloseMemHandle(n->dp_peer[r]);
+        n->dp_peer[r] = nullptr;
+    }
+    cudaFree(n->dp_local);
+    n->dp_local = nullptr; n->dp_world = 1; n->dp_rank = 0;
+}
+
 static void free_all(Net* n) {
     cudaFree(n->master); cudaFree(n->params); cudaFree(n->ema); cudaFree(n->grads);
     cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps); cudaFree(n->params_img); cudaFree(n->barrier_counter);
     n->params_img = nullptr; n->barrier_counter = nullptr; n->barrier_total = 0;
     cudaFree(n->timeline); n->timeline = nullptr;
+    dp_teardown(n);
     cudaFree(n->partials); cudaFree(n->grid_grad); cudaFree(n->loss_partials); cudaFree(n->grad_f32); cudaFree(n->loss_d);
     if (n->loss_pinned) cudaFreeHost(n->loss_pinned);
     n->master = nullptr; n->params = nullptr; n->ema = nullptr; n->grads = nullptr; n->m1 = n->m2 = nullptr;
@@ -361,6 +374,14 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.ema_debias_new = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)h->step));
     a.apply = apply;
     a.timeline = h->timeline;
+    a.dp_world = 1; a.dp_rank = 0; a.dp_step = h->step; a.x_stride = h->x_stride;
+    if (apply && h->dp_world > 1) {
+        a.dp_world = (uint32_t)h->dp_world; a.dp_rank = (uint32_t)h->dp_rank;
+        for (int r = 0; r < h->dp_world; ++r) {
+            a.xbuf[r] = (float*)h->dp_peer[r];
+            a.xflag[r] = (uint32_t*)((char*)h->dp_peer[r] + h->xbuf_bytes);
+        }
+    }
     return a;
 }
 
@@ -428,6 +449,64 @@ int nrc_b200_train_host(nrc_b200_handle h, const float* q_h, const float* t_h, f
     CU(cudaMemcpyAsync(h->train_in_d, q_h, (size_t)NRC_B200_BATCH_SIZE * 60, cudaMemcpyHostToDevice, h->stream));
     CU(cudaMemcpyAsync(h->train_tgt_d, t_h, (size_t)NRC_B200_BATCH_SIZE * 12, cudaMemcpyHostToDevice, h->stream));
     return nrc_b200_train(h, h->train_in_d, h->train_tgt_d, nullptr, loss_h);
+}
+
+// ---------------------------------------------------------------- data-parallel training over NVLink peer memory
+// Step 1 (every rank): allocate the exchange buffer and export its CUDA IPC handle (64 bytes).
+int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out) {
+    if (!h || h->destroyed || !ipc_handle_out) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    CU(cudaStreamSynchronize(h->stream));
+    dp_teardown(h);
+    // per (parity, source rank) row: [(n_mlp + 1 -> 32) tagged float2 slots | n_grid floats]  (nrc_train.cu phase 3)
+    h->x_stride = 2 * ((h->n_mlp + 1 + 31) / 32 * 32) + ((h->n_params - h->n_mlp) + 31) / 32 * 32;
+    h->xbuf_bytes = (size_t)2 * kMaxDpRanks * h->x_stride * sizeof(float);
+    const size_t flag_bytes = (size_t)2 * kMaxDpRanks * 128 * sizeof(uint32_t);
+    CU(cudaMalloc(&h->dp_local, h->xbuf_bytes + flag_bytes));
+    CU(cudaMemset(h->dp_local, 0, h->xbuf_bytes + flag_bytes));
+    CU(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t mh;
+    CU(cudaIpcGetMemHandle(&mh, h->dp_local));
+    static_assert(sizeof(mh) == NRC_B200_IPC_HANDLE_BYTES, "IPC handle size");
+    memcpy(ipc_handle_out, &mh, sizeof(mh));
+    return NRC_B200_OK;
+}
+// Step 2 (every rank, after an all-gather of the handles): map the peers' buffers.  The optimizer state must be
+// identical on all ranks (same seed / same nrc_b200_load_master) and the step counters equal.
+int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_handles) {
+    if (!h || h->destroyed || !ipc_handles) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    if (world < 1 || world > kMaxDpRanks || rank < 0 || rank >= world) return fail(NRC_B200_ERR_INVALID, "bad rank/world");
+    if (!h->dp_local) return fail(NRC_B200_ERR_INVALID, "nrc_b200_dp_export must be called first");
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) { h->dp_peer[r] = h->dp_local; continue; }
+        cudaIpcMemHandle_t mh;
+        memcpy(&mh, (const char*)ipc_handles + (size_t)r * sizeof(mh), sizeof(mh));
+        CU(cudaIpcOpenMemHandle(&h->dp_peer[r], mh, cudaIpcMemLazyEnablePeerAccess));
+    }
+    h->dp_rank = rank; h->dp_world = world;
+    return NRC_B200_OK;
+}
+// One optimizer step on a global batch of n_global samples of which this rank holds n_local: ONE cooperative kernel
+// per rank does forward/backward, the gradient all-reduce (peer stores + flags over NVLink) and Adam + EMA.
+// Every rank must call it for every step; loss_h (optional, blocks) receives the global loss.
+int nrc_b200_train_dp(nrc_b200_handle h, const float* q, const float* t, uint32_t n_local, uint32_t n_global,
+                      void* cu_stream, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
+        return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
+    h->step += 1;
+    h->barrier_total += n_local / 128;
+    CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/1), h->gm, h->stream));
+    h->launches += 1;
+    h->pending_tiles = 0;
+    if (loss_h) {
+        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        *loss_h = *h->loss_pinned;
+    }
+    return NRC_B200_OK;
 }
 
 // Debug: per-tile clock64 stamps of the last training step [128 tiles][8 slots]:

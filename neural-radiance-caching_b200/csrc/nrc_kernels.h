@@ -35,7 +35,17 @@ struct TrainArgs {
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale, ema_debias_old, ema_debias_new;
     int apply;
     long long* timeline;             // optional [n_tiles][8] clock64 stamps of the phases (debug), or nullptr
+    // Data-parallel exchange fused into phase 3 (dp_world > 1, apply = 1): every rank pushes its slice gradients into
+    // row `dp_rank` of EVERY peer's exchange buffer through NVLink peer pointers and sums the rows it received in rank
+    // order (bit-identical replicas, no NCCL call).  MLP slice + loss: (value, step) pairs in 8-byte stores, polled by
+    // the receiver; grid part: floats + fence + per-slice flag.
+    //   xbuf[r]  : rank r's buffer  float[2 parities][dp_world][x_stride]   (xbuf[dp_rank] is local memory)
+    //   xflag[r] : rank r's flags   u32  [2 parities][dp_world][128 slices] (value = step number)
+    uint32_t dp_world, dp_rank, dp_step, x_stride;
+    float* xbuf[8];
+    uint32_t* xflag[8];
 };
+constexpr int kMaxDpRanks = 8;
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream);
 
 // Adam + EMA from an already reduced fp32 gradient (after a data-parallel all-reduce); clears grid_grad.

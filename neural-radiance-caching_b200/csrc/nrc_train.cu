@@ -434,29 +434,114 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             scratch[w] = acc;
         }
         __syncthreads();
-        for (uint32_t j = tid; j < hi - lo; j += kTrainThreads) {
-            const float* sc = reinterpret_cast<const float*>(scratch);
+        const float* sc = reinterpret_cast<const float*>(scratch);
+        auto slice_grad = [&](uint32_t j) {     // local gradient of parameter lo + j: groups summed in fixed order
             float gsum = 0.0f;
             for (uint32_t g = 0; g < groups; ++g) gsum += sc[(g * ncol4 + (j >> 2)) * 4 + (j & 3)];
-            a.grad_f32[lo + j] = gsum;
-            if (a.apply) adam_ema_param(a, lo + j, gsum, E);
-        }
-        if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
-            const uint32_t n_grid = a.n_params - NMLP;
-            const uint32_t SG = (n_grid + n_tiles - 1) / n_tiles;
-            const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
-            for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
-                const float g = __ldcg(a.grid_grad + j);
-                a.grad_f32[NMLP + j] = g;
-                if (a.apply) { adam_ema_param(a, NMLP + j, g, E); a.grid_grad[j] = 0.0f; }
+            return gsum;
+        };
+        const uint32_t n_grid = a.n_params - NMLP;
+        const uint32_t SG = (n_grid + n_tiles - 1) / n_tiles;
+        const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
+        const uint32_t R = a.dp_world, me = a.dp_rank;
+        if (!(a.apply && R > 1)) {
+            // ---- single GPU (or gradient-only for an external all-reduce)
+            for (uint32_t j = tid; j < hi - lo; j += kTrainThreads) {
+                const float g = slice_grad(j);
+                a.grad_f32[lo + j] = g;
+                if (a.apply) adam_ema_param(a, lo + j, g, E);
             }
-        }
-        if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
-            float l = 0.0f;
-            for (uint32_t t = lane; t < n_tiles; t += 32) l += __ldcg(a.loss_partials + t);
+            if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
+                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
+                    const float g = __ldcg(a.grid_grad + j);
+                    a.grad_f32[NMLP + j] = g;
+                    if (a.apply) { adam_ema_param(a, NMLP + j, g, E); a.grid_grad[j] = 0.0f; }
+                }
+            }
+            if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
+                float l = 0.0f;
+                for (uint32_t t = lane; t < n_tiles; t += 32) l += __ldcg(a.loss_partials + t);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-            if (lane == 0) *a.loss_out = l;
+                for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+                if (lane == 0) *a.loss_out = l;
+            }
+        } else {
+            // ---- data parallel: the all-reduce happens here, over NVLink peer memory.
+            // MLP slice + loss use a low-latency protocol: every 8-byte store carries (value, step tag), so the
+            // receiver polls the data words themselves -- no fence, no separate flag, one NVLink one-way latency.
+            // The (large) grid part is pushed as plain floats, then fence + one flag per slice.
+            const uint32_t par = a.dp_step & 1;
+            const uint32_t LLS = (NMLP + 1 + 31) & ~31u;                        // float2 slots of the tagged region
+            auto row = [&](uint32_t dst, uint32_t src) { return a.xbuf[dst] + ((size_t)par * R + src) * a.x_stride; };
+            const float tag = __uint_as_float(a.dp_step);
+            float g_mine[2] = {0.0f, 0.0f};                                       // <= 2 slice elements per thread
+            for (uint32_t j = tid, u = 0; j < hi - lo; j += kTrainThreads, ++u) {
+                const float g = slice_grad(j);
+                if (u < 2) g_mine[u] = g;
+                for (uint32_t r = 0; r < R; ++r)
+                    if (r != me || u >= 2)
+                        asm volatile("st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(reinterpret_cast<float2*>(row(r, me)) + lo + j), "f"(g), "f"(tag) : "memory");
+            }
+            float l_mine = 0.0f;
+            if (tile == 0 && warp == 0) {
+                for (uint32_t t = lane; t < n_tiles; t += 32) l_mine += __ldcg(a.loss_partials + t);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) l_mine += __shfl_xor_sync(0xffffffffu, l_mine, o);
+                if (lane == 0)
+                    for (uint32_t r = 0; r < R; ++r)
+                        if (r != me) asm volatile("st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(reinterpret_cast<float2*>(row(r, me)) + NMLP), "f"(l_mine), "f"(tag) : "memory");
+            }
+            if constexpr (ENC == 1) {
+                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
+                    const float g = __ldcg(a.grid_grad + j);
+                    a.grid_grad[j] = 0.0f;
+                    for (uint32_t r = 0; r < R; ++r) row(r, me)[2 * LLS + j] = g;
+                }
+                __threadfence_system();
+                __syncthreads();
+                if ((uint32_t)tid < R && (uint32_t)tid != me) {
+                    uint32_t* f = a.xflag[tid] + ((size_t)par * R + me) * 128 + tile;
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.dp_step) : "memory");
+                }
+            }
+            auto poll = [&](const float2* p) {      // tagged word of a peer for this step
+                float2 v;
+                uint32_t spins = 0;
+                do {
+                    asm volatile("ld.relaxed.sys.global.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p) : "memory");
+                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+                } while (__float_as_uint(v.y) != a.dp_step);
+                return v.x;
+            };
+            for (uint32_t j = tid, u = 0; j < hi - lo; j += kTrainThreads, ++u) {
+                float g = 0.0f;
+                for (uint32_t r = 0; r < R; ++r)     // rank order: identical sums on every rank
+                    g += (r == me && u < 2) ? g_mine[u] : poll(reinterpret_cast<const float2*>(row(me, r)) + lo + j);
+                a.grad_f32[lo + j] = g;
+                adam_ema_param(a, lo + j, g, E);
+            }
+            if (tile == 0 && tid == 0) {
+                float l = 0.0f;
+                for (uint32_t r = 0; r < R; ++r) l += r == me ? l_mine : poll(reinterpret_cast<const float2*>(row(me, r)) + NMLP);
+                *a.loss_out = l;
+            }
+            if constexpr (ENC == 1) {
+                if ((uint32_t)tid < R && (uint32_t)tid != me) {
+                    const uint32_t* w = a.xflag[me] + ((size_t)par * R + tid) * 128 + tile;
+                    uint32_t seen, spins = 0;
+                    do {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(w) : "memory");
+                        if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+                    } while ((int32_t)(seen - a.dp_step) < 0);
+                }
+                __syncthreads();
+                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
+                    float g = 0.0f;
+                    for (uint32_t r = 0; r < R; ++r) g += __ldcv(row(me, r) + 2 * LLS + j);
+                    a.grad_f32[NMLP + j] = g;
+                    adam_ema_param(a, NMLP + j, g, E);
+                }
+            }
         }
     }
     __syncthreads();

@@ -26,13 +26,23 @@ class _DevPtr:
 
 
 class DataParallelTrainer:
-    """Drives `net` (nrc_b200.Network, or any object with train_grad / train_apply / n_params) data-parallel."""
+    """Drives `net` (nrc_b200.Network, or any object with train_grad / train_apply / n_params) data-parallel.
 
-    def __init__(self, net, group=None):
-        self.net, self.group = net, group
+    mode "nccl":  backward kernel -> torch.distributed all-reduce (NCCL / gloo) -> Adam+EMA kernel.
+    mode "fused": ONE kernel per rank and step; the all-reduce happens inside it through NVLink peer memory
+                  (nrc_b200_dp_export / _connect / _train_dp; CUDA IPC handles are all-gathered here once)."""
+
+    def __init__(self, net, group=None, mode="nccl"):
+        self.net, self.group, self.mode = net, group, mode
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._views = {}
+        if mode == "fused" and self.world > 1:
+            mine = net.dp_export()
+            handles = [None] * self.world
+            dist.all_gather_object(handles, mine, group=group)
+            net.dp_connect(self.rank, self.world, b"".join(handles))
+            dist.barrier(group=group)      # every rank has mapped every buffer before the first push
 
     def _grad_tensor(self, g):
         if isinstance(g, torch.Tensor):
@@ -44,6 +54,8 @@ class DataParallelTrainer:
     def train(self, inputs, targets, n_local, stream=None, want_loss=False):
         """One optimizer step on a global batch of world*n_local samples; `inputs`/`targets` are this rank's shard."""
         n_global = n_local * self.world
+        if self.mode == "fused" and self.world > 1:
+            return self.net.train_dp(inputs, targets, n_local, n_global, stream, want_loss=want_loss)
         g = self._grad_tensor(self.net.train_grad(inputs, targets, n_local, n_global, stream))
         if self.world > 1:
             dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
