@@ -120,6 +120,77 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
     a.ema[i] = __float2half_rn(filtered);
 }
 
+// Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
+// in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
+__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E) {
+    for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 8 * kTrainThreads) {
+        float4 g[2], w[2], m1[2], m2[2];
+        uint4 st[2];
+        uint2 em[2], pr[2];
+        bool live[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const uint32_t j = j0 + u * 4 * kTrainThreads;
+            live[u] = j < ghi;
+            if (live[u]) {
+                const uint32_t i = base + j;
+                g[u] = __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j));
+                w[u] = *reinterpret_cast<const float4*>(a.master + i);
+                m1[u] = *reinterpret_cast<const float4*>(a.m1 + i);
+                m2[u] = *reinterpret_cast<const float4*>(a.m2 + i);
+                st[u] = *reinterpret_cast<const uint4*>(a.steps + i);
+                em[u] = *reinterpret_cast<const uint2*>(a.ema + i);
+                pr[u] = *reinterpret_cast<const uint2*>(a.params + i);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            if (!live[u]) continue;
+            const uint32_t j = j0 + u * 4 * kTrainThreads, i = base + j;
+            float gv[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, wv[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+            float av[4] = {m1[u].x, m1[u].y, m1[u].z, m1[u].w}, bv[4] = {m2[u].x, m2[u].y, m2[u].z, m2[u].w};
+            uint32_t sv[4] = {st[u].x, st[u].y, st[u].z, st[u].w};
+            __half ev[4], pv[4], gh[4];
+            *reinterpret_cast<uint2*>(ev) = em[u];
+            *reinterpret_cast<uint2*>(pv) = pr[u];
+            bool any = false;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                gh[c] = __float2half_rn(gv[c]);
+                const float gradient = __half2float(gh[c]) / a.loss_scale;
+                if (gradient != 0.0f) {       // adam.h:80-82: grid parameters without gradient are skipped entirely
+                    any = true;
+                    av[c] = a.beta1 * av[c] + (1.0f - a.beta1) * gradient;
+                    bv[c] = a.beta2 * bv[c] + (1.0f - a.beta2) * (gradient * gradient);
+                    const uint32_t cur = ++sv[c];
+                    const float lr = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+                    const float eff = fminf(fmaxf(lr / (sqrtf(bv[c]) + a.eps), 0.0f), 3.402823466e+38f);
+                    wv[c] = wv[c] - eff * av[c];
+                    pv[c] = __float2half_rn(wv[c]);
+                }
+                const float filtered = (__half2float(ev[c]) * a.ema_decay * a.ema_debias_old +
+                                        __half2float(pv[c]) * (1.0f - a.ema_decay)) * a.ema_debias_new;
+                ev[c] = __float2half_rn(filtered);
+            }
+            *reinterpret_cast<float4*>(a.grad_f32 + i) = g[u];
+            *reinterpret_cast<uint2*>(a.grads + i) = *reinterpret_cast<uint2*>(gh);
+            *reinterpret_cast<uint2*>(a.ema + i) = *reinterpret_cast<uint2*>(ev);
+            if (any) {
+                *reinterpret_cast<float4*>(a.master + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+                *reinterpret_cast<float4*>(a.m1 + i) = make_float4(av[0], av[1], av[2], av[3]);
+                *reinterpret_cast<float4*>(a.m2 + i) = make_float4(bv[0], bv[1], bv[2], bv[3]);
+                *reinterpret_cast<uint4*>(a.steps + i) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
+                *reinterpret_cast<uint2*>(a.params + i) = *reinterpret_cast<uint2*>(pv);
+            }
+            if (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f)   // also gradients that round to 0 in fp16
+                *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+    }
+}
+
+#ifndef NRCB_SCATTER_AGG
+#define NRCB_SCATTER_AGG 1
+#endif
 // ---------------------------------------------------------------- the step kernel
 template <int ENC>
 __global__ void __launch_bounds__(kTrainThreads, 1)
@@ -317,7 +388,22 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         wait_mma();
         stamp(3);
         if (warp == 0 && lane == 0) a.loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
-        if constexpr (ENC == 1) {   // grid gradient scatter: half hf handles levels 8*hf .. 8*hf+7 (columns 16*hf ..)
+        if constexpr (ENC == 1) {
+            // Grid gradient scatter (grid.h:252-255,301-319): half hf handles levels 8*hf .. 8*hf+7 (columns 16*hf ..).
+            // The coarse levels (half 0) are pre-aggregated per tile in a shared-memory table keyed by the entry index:
+            // a concentrated scene (the Cornell box spans 0.1 of the unit cube) sends all 16384 x 8 corner updates of a
+            // coarse level to a few dozen entries, which serialises global atomics in L2 (33 us measured).  After the
+            // aggregation every CTA issues one global red per DISTINCT entry it touched.
+            constexpr uint32_t kSlots = 2048, kEmpty = 0xFFFFFFFFu;
+            uint32_t* s_tag = reinterpret_cast<uint32_t*>(smem + L::kH);            // [kSlots]   (activations are dead now)
+            int* s_acc = reinterpret_cast<int*>(smem + L::kH + kSlots * 4);          // [kSlots][2] fixed point
+            uint32_t* s_max = reinterpret_cast<uint32_t*>(smem + L::kH + kSlots * 12); // tile maximum of |dL/dy| (float bits)
+            const int htid = qd * 32 + lane;                                          // 0..127 inside the half
+            if (hf == 0) {
+                for (uint32_t sl = htid; sl < kSlots; sl += 128) { s_tag[sl] = kEmpty; s_acc[2 * sl] = 0; s_acc[2 * sl + 1] = 0; }
+                if (htid == 0) *s_max = 0;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
             uint32_t v[16];
             tmem_ld16(tq + kAcc + hf * 16, v);
             tmem_wait_ld();
@@ -326,9 +412,19 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 const int lv = hf * 8 + j;
                 const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * j])));
                 const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * j + 1])));
-                if (g0 == 0.0f && g1 == 0.0f) continue;
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], res = gm.resolution[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
+                float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
+                const bool active = g0 != 0.0f || g1 != 0.0f;
+                float S = 0.0f, Sinv = 0.0f;
+                if (hf == 0 && NRCB_SCATTER_AGG) {   // common scale of this level for the whole tile
+                    const uint32_t mx = __reduce_max_sync(0xffffffffu, max(__float_as_uint(fabsf(g0)), __float_as_uint(fabsf(g1))));
+                    if (lane == 0) atomicMax(s_max, mx);
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    const uint32_t eb = max(*s_max >> 23, 24u);
+                    S = __uint_as_float((273u - eb) << 23);
+                    Sinv = __uint_as_float((eb - 19u) << 23);
+                }
                 float p[3];
                 uint32_t gp[3];
 #pragma unroll
@@ -338,7 +434,6 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     gp[d] = (uint32_t)(int)fl;
                     p[d] -= fl;
                 }
-                float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     float wgt = 1.0f;
@@ -350,10 +445,43 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     const uint32_t idx = (dense ? cc[0] + cc[1] * res + cc[2] * res * res
                                                 : cc[0] ^ (cc[1] * 2654435761u) ^ (cc[2] * 805459861u)) & (size - 1);
                     const float wh = __half2float(__float2half_rn(wgt));   // (GRAD_T)weight, grid.h:254
-                    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(wh * g0), "f"(wh * g1) : "memory");
+                    float v0 = active ? wh * g0 : 0.0f, v1 = active ? wh * g1 : 0.0f;
+                    if (hf != 0 || !NRCB_SCATTER_AGG) {
+                        if (active) asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
+                        continue;
+                    }
+                    // CTA-level aggregation in a shared-memory table of FIXED-POINT accumulators: 32-bit integer atomics are
+                    // native in shared memory (ATOMS.ADD; float / 64-bit adds compile to CAS spin loops that collapse
+                    // under same-address conflicts).  Scale: 20 bits below the largest |dL/dy| of the tile at this level,
+                    // 1024 terms of headroom.
+                    if (!active) continue;
+                    const uint32_t sl = idx & (kSlots - 1);
+                    const uint32_t old = atomicCAS(&s_tag[sl], kEmpty, idx);
+                    if (old == kEmpty || old == idx) {
+                        atomicAdd(&s_acc[2 * sl], __float2int_rn(v0 * S));
+                        atomicAdd(&s_acc[2 * sl + 1], __float2int_rn(v1 * S));
+                    } else {
+                        asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
+                    }
                 }
+                if (hf == 0) {   // flush the table of this level: one global red per distinct entry
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    for (uint32_t sl = htid; sl < kSlots; sl += 128) {
+                        const uint32_t tg_ = s_tag[sl];
+                        if (tg_ != kEmpty) {
+                            asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * tg_), "f"((float)s_acc[2 * sl] * Sinv), "f"((float)s_acc[2 * sl + 1] * Sinv) : "memory");
+                            s_tag[sl] = kEmpty; s_acc[2 * sl] = 0; s_acc[2 * sl + 1] = 0;
+                        }
+                    }
+                    if (htid == 0) *s_max = 0;
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+#ifdef NRCB_DEBUG_LEVELS
+                if (a.timeline && tid == 0) a.timeline[tile * 8 + j] = clock64();
+#endif
             }
         }
+        if (a.timeline && tid == 128) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
         // per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.
         // The TMEM loads are warp-wide (.sync.aligned): every lane executes them, lanes 0..15 store.
         // Column chunks of 16 are split between the two halves.
@@ -441,7 +569,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             return gsum;
         };
         const uint32_t n_grid = a.n_params - NMLP;
-        const uint32_t SG = (n_grid + n_tiles - 1) / n_tiles;
+        const uint32_t SG = ((n_grid + n_tiles - 1) / n_tiles + 3) & ~3u;   // multiple of 4: float4 groups
         const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
         const uint32_t R = a.dp_world, me = a.dp_rank;
         if (!(a.apply && R > 1)) {
@@ -452,11 +580,9 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 if (a.apply) adam_ema_param(a, lo + j, g, E);
             }
             if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
-                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
-                    const float g = __ldcg(a.grid_grad + j);
-                    a.grad_f32[NMLP + j] = g;
-                    if (a.apply) { adam_ema_param(a, NMLP + j, g, E); a.grid_grad[j] = 0.0f; }
-                }
+                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E);
+                else
+                    for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) a.grad_f32[NMLP + j] = __ldcg(a.grid_grad + j);
             }
             if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
                 float l = 0.0f;

@@ -17,7 +17,8 @@ for enc in (0, 1):
     d = np.diff(tl[:, :7], axis=1) / 1.965e3   # us at 1965 MHz
     names = ["setup+encode", "forward", "backward+wgrad", "scatter+dump", "grid barrier", "reduce+adam"]
     print("enc", enc, " ".join(f"{n}={np.median(d[:, i]):.2f}us(max {d[:, i].max():.2f})" for i, n in enumerate(names)),
-          f"total={np.median(tl[:, 6] - tl[:, 0]) / 1.965e3:.2f}us")
+          f"total={np.median(tl[:, 6] - tl[:, 0]) / 1.965e3:.2f}us",
+          f"half1-scatter-done at +{np.median(tl[:, 7] - tl[:, 3]) / 1.965e3:.2f}us after backward")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     net.debug_train_timeline(False)
     torch.cuda.synchronize(); e0.record()
