@@ -92,6 +92,61 @@ int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_
 int nrc_b200_train_dp(nrc_b200_handle h, const float* queries_d, const float* targets_d, uint32_t n_local,
                       uint32_t n_global, void* cu_stream, float* loss_h);
 
+/* ---- NEXT rows: the helper kernels either side of the network in Device::render ----------- */
+typedef struct nrc_b200_training_record {       /* nrc::TrainingRecord, neural_radiance_caching.h:57-78 (28 bytes) */
+    int propTo;                                  /* next record along the radiance propagation, < 0 = end */
+    float localThroughput[3];
+    int pixelIndex, tileIndex, propLength;       /* debug fields, carried but unused */
+} nrc_b200_training_record;
+typedef struct nrc_b200_suffix_end_vertex {      /* nrc::TrainingSuffixEndVertex, neural_radiance_caching.h:81-98 (16 bytes) */
+    int startTrainRecord;
+    float radianceMask;                          /* 1 = self-training, 0 = unbiased */
+    int pixelIndex, tileIndex;
+} nrc_b200_suffix_end_vertex;
+typedef struct nrc_b200_training_stat { float loss; int num_train_records; } nrc_b200_training_stat;   /* nrc::TrainingStat */
+
+/* accumulate_render_radiance (nrc_helpers.cu:77-129, launched by Device::nrcAccumulateRadiance, Device.cpp:1310-1337).
+ * render_mode = nrc::RenderMode (0 Full, 1 NoCache, 2 CacheOnly, 3 CacheFirstVertex, 4 DebugCacheNoThroughputModulation,
+ * 5 DebugThroughputOnly); output is a float4-per-pixel device buffer (the reference's GL-interop surface, headless). */
+int nrc_b200_accumulate_render_radiance(const float* radiance_d, const float* throughput_d, float* output_rgba_d,
+                                        uint32_t n_pixels, int render_mode, uint32_t iteration_index, void* cu_stream);
+/* propagate_train_radiance (nrc_helpers.cu:131-224, Device::nrcPropagateRadiance, Device.cpp:1382-1417): per tile,
+ * targets[i] += localThroughput[i] * radiance along the propTo chain starting at end_vertices[tile].startTrainRecord. */
+int nrc_b200_propagate_train_radiance(const nrc_b200_suffix_end_vertex* end_vertices_d, const float* end_radiance_d,
+                                      const nrc_b200_training_record* records_d, float* targets_d, uint32_t n_tiles,
+                                      void* cu_stream);
+/* generateRandomPermutationForTrain + permute_train_data (NRCUtil.cu:20-35, nrc_helpers.cu:226-249): dst[d] =
+ * src[permutation(d, seed) % min(num_records, 65536)], d < 65536.  The permutation is a keyed 16-bit bijection
+ * (nrc_b200_permutation) instead of cuRAND keys + a CUB radix sort. */
+uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed);
+int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
+                                int num_records, uint32_t seed, void* cu_stream);
+/* Fused: the training step on batch `batch_index` (0..3) of the permuted data without materialising it; identical
+ * result to nrc_b200_permute_train_data followed by nrc_b200_train on dst + batch_index*16384. */
+int nrc_b200_train_shuffled(nrc_b200_handle h, const float* q_src_d, const float* t_src_d, int num_records, uint32_t seed,
+                            uint32_t batch_index, void* cu_stream, float* loss_h);
+/* Device::adjustTileSize (Device.cpp:818-828), host side. */
+void nrc_b200_adjust_tile_size(int tile_x, int tile_y, int num_train_records, int* new_x, int* new_y);
+
+/* Frame driver: the NRC sequence of Device::render (Device.cpp:2495-2515) in one call, everything asynchronous on the
+ * handle's stream; stat != NULL reads the mean loss of the four steps back once (one synchronisation). */
+typedef struct nrc_b200_frame {
+    const float* queries_d;          /* RadianceQuery[num_pixels + num_tiles]  (bufDynamic.radianceQueriesInference) */
+    float* results_d;                /* float3[num_pixels + num_tiles]         (bufDynamic.radianceResultsInference) */
+    uint32_t num_pixels, num_tiles;
+    const float* throughput_d;       /* float3[num_pixels] lastRenderThroughput, NULL = no accumulation */
+    float* output_rgba_d;            /* float4[num_pixels] output buffer */
+    int render_mode;                 /* nrc::RenderMode */
+    uint32_t iteration_index;
+    const nrc_b200_suffix_end_vertex* end_vertices_d;   /* [num_tiles] */
+    const nrc_b200_training_record* records_d;          /* [65536] */
+    const float* train_queries_d;    /* RadianceQuery[65536] (unshuffled, buffer 0) */
+    float* train_targets_d;          /* float3[65536] (unshuffled; propagation adds into it) */
+    int num_train_records;
+    uint32_t shuffle_seed;           /* e.g. the frame index */
+} nrc_b200_frame;
+int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* frame, void* cu_stream, nrc_b200_training_stat* stat);
+
 /* Parity-harness access to the parameters (Trainer::params() / set_params(), trainer.h:226-269). */
 typedef enum nrc_b200_param_kind {
     NRC_B200_PARAMS_MASTER_F32 = 0,  /* fp32 master weights  */

@@ -32,7 +32,25 @@ ABI_SYMBOLS = [
     "nrc_b200_infer_host", "nrc_b200_train_host", "nrc_b200_last_loss_device", "nrc_b200_train_grad", "nrc_b200_train_apply",
     "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
     "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline", "nrc_b200_dp_export", "nrc_b200_dp_connect", "nrc_b200_train_dp",
+    "nrc_b200_accumulate_render_radiance", "nrc_b200_propagate_train_radiance", "nrc_b200_permutation",
+    "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_adjust_tile_size", "nrc_b200_update",
 ]
+
+
+# nrc::RenderMode (neural_radiance_caching.h:13-22)
+RENDER_FULL, RENDER_NO_CACHE, RENDER_CACHE_ONLY, RENDER_CACHE_FIRST_VERTEX, RENDER_DEBUG_NO_THROUGHPUT, RENDER_DEBUG_THROUGHPUT = range(6)
+
+
+class Frame(ctypes.Structure):       # nrc_b200_frame
+    _fields_ = [("queries_d", ctypes.c_void_p), ("results_d", ctypes.c_void_p), ("num_pixels", ctypes.c_uint32),
+                ("num_tiles", ctypes.c_uint32), ("throughput_d", ctypes.c_void_p), ("output_rgba_d", ctypes.c_void_p),
+                ("render_mode", ctypes.c_int), ("iteration_index", ctypes.c_uint32), ("end_vertices_d", ctypes.c_void_p),
+                ("records_d", ctypes.c_void_p), ("train_queries_d", ctypes.c_void_p), ("train_targets_d", ctypes.c_void_p),
+                ("num_train_records", ctypes.c_int), ("shuffle_seed", ctypes.c_uint32)]
+
+
+class TrainingStat(ctypes.Structure):   # nrc::TrainingStat, NRCNetwork.h:15-18
+    _fields_ = [("loss", ctypes.c_float), ("num_train_records", ctypes.c_int)]
 
 
 def build(verbose=False):
@@ -78,6 +96,15 @@ def lib():
         L.nrc_b200_last_error.restype = ctypes.c_char_p
         L.nrc_b200_launch_count.argtypes = [vp, P(u64)]
         L.nrc_b200_debug_train_timeline.argtypes = [vp, i32, vp]
+        L.nrc_b200_accumulate_render_radiance.argtypes = [vp, vp, vp, u32, i32, u32, vp]
+        L.nrc_b200_propagate_train_radiance.argtypes = [vp, vp, vp, vp, u32, vp]
+        L.nrc_b200_permutation.argtypes = [u32, u32]
+        L.nrc_b200_permutation.restype = u32
+        L.nrc_b200_permute_train_data.argtypes = [vp, vp, vp, vp, i32, u32, vp]
+        L.nrc_b200_train_shuffled.argtypes = [vp, vp, vp, i32, u32, u32, vp, P(f32)]
+        L.nrc_b200_adjust_tile_size.argtypes = [i32, i32, i32, P(i32), P(i32)]
+        L.nrc_b200_adjust_tile_size.restype = None
+        L.nrc_b200_update.argtypes = [vp, P(Frame), vp, P(TrainingStat)]
         L.nrc_b200_dp_export.argtypes = [vp, vp]
         L.nrc_b200_dp_connect.argtypes = [vp, i32, i32, vp]
         L.nrc_b200_train_dp.argtypes = [vp, vp, vp, u32, u32, vp, P(f32)]
@@ -105,6 +132,31 @@ def _check(rc):
     if rc == -1:
         raise ValueError(msg)    # std::invalid_argument (NRCNetworkConfigs.h:129-131)
     raise RuntimeError(msg)      # std::runtime_error (CUDA_CHECK_THROW)
+
+
+def accumulate_render_radiance(radiance_d, throughput_d, output_rgba_d, n_pixels, render_mode, iteration_index, stream=None):
+    _check(lib().nrc_b200_accumulate_render_radiance(_ptr(radiance_d), _ptr(throughput_d), _ptr(output_rgba_d), int(n_pixels),
+                                                     int(render_mode), int(iteration_index), _ptr(stream)))
+
+
+def propagate_train_radiance(end_vertices_d, end_radiance_d, records_d, targets_d, n_tiles, stream=None):
+    _check(lib().nrc_b200_propagate_train_radiance(_ptr(end_vertices_d), _ptr(end_radiance_d), _ptr(records_d),
+                                                   _ptr(targets_d), int(n_tiles), _ptr(stream)))
+
+
+def permute_train_data(q_src_d, t_src_d, q_dst_d, t_dst_d, num_records, seed, stream=None):
+    _check(lib().nrc_b200_permute_train_data(_ptr(q_src_d), _ptr(t_src_d), _ptr(q_dst_d), _ptr(t_dst_d), int(num_records),
+                                             int(seed), _ptr(stream)))
+
+
+def permutation(i, seed):
+    return lib().nrc_b200_permutation(int(i), int(seed))
+
+
+def adjust_tile_size(tile_x, tile_y, num_train_records):
+    x, y = ctypes.c_int(), ctypes.c_int()
+    lib().nrc_b200_adjust_tile_size(int(tile_x), int(tile_y), int(num_train_records), ctypes.byref(x), ctypes.byref(y))
+    return x.value, y.value
 
 
 class HyperParams:               # nrc::HyperParams, NRCNetwork.h:10-13
@@ -200,6 +252,19 @@ class Network:
         _check(lib().nrc_b200_train_dp(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global), _ptr(stream),
                                        ctypes.byref(loss) if want_loss else None))
         return loss.value if want_loss else None
+
+    # ---- NEXT rows: the per-frame sequence around the network (Device::render) ------------------------------
+    def train_shuffled(self, q_src_d, t_src_d, num_records, seed, batch_index, stream=None, want_loss=False):
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train_shuffled(self._h, _ptr(q_src_d), _ptr(t_src_d), int(num_records), int(seed),
+                                             int(batch_index), _ptr(stream), ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
+
+    def update(self, frame, stream=None, want_stat=False):
+        """frame: nrc_b200.Frame.  Returns TrainingStat when want_stat (one synchronisation), else None."""
+        stat = TrainingStat()
+        _check(lib().nrc_b200_update(self._h, ctypes.byref(frame), _ptr(stream), ctypes.byref(stat) if want_stat else None))
+        return stat if want_stat else None
 
     def last_loss_device(self):
         p = ctypes.c_void_p()

@@ -6,6 +6,8 @@
 #include "../../include/nrc_b200.h"
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
+#include "nrc_frame.cuh"
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -43,7 +45,8 @@ struct nrc_b200_network {
     // training scratch (device)
     float* partials = nullptr; float* grid_grad = nullptr; float* loss_partials = nullptr;
     float* grad_f32 = nullptr; float* loss_d = nullptr;
-    float* loss_pinned = nullptr;
+    float* loss_pinned = nullptr;   // 4 floats (one per batch of a frame)
+    float* loss4_d = nullptr;
     // hyper-parameters (NRCNetworkConfigs.h:18-24,43-47,92-97; adam.h defaults)
     float lr = 1e-3f, beta1 = 0.9f, beta2 = 0.999f, eps = 1e-8f, l2_reg = 1e-6f, ema_decay = 0.99f, loss_scale = 128.0f;
     uint32_t step = 0;
@@ -113,6 +116,7 @@ static void free_all(Net* n) {
     dp_teardown(n);
     cudaFree(n->partials); cudaFree(n->grid_grad); cudaFree(n->loss_partials); cudaFree(n->grad_f32); cudaFree(n->loss_d);
     if (n->loss_pinned) cudaFreeHost(n->loss_pinned);
+    cudaFree(n->loss4_d); n->loss4_d = nullptr;
     n->master = nullptr; n->params = nullptr; n->ema = nullptr; n->grads = nullptr; n->m1 = n->m2 = nullptr;
     n->steps = nullptr; n->partials = n->grid_grad = n->loss_partials = n->grad_f32 = n->loss_d = nullptr;
     n->loss_pinned = nullptr;
@@ -170,7 +174,9 @@ static int build_model(Net* n) {
     CU(cudaMalloc(&n->loss_partials, kMaxTrainTiles * 4));
     CU(cudaMalloc(&n->loss_d, 4));
     if (P > n->n_mlp) CU(cudaMalloc(&n->grid_grad, (P - n->n_mlp) * 4));
-    CU(cudaMallocHost(&n->loss_pinned, 4));
+    CU(cudaMallocHost(&n->loss_pinned, 16));
+    CU(cudaMalloc(&n->loss4_d, 16));
+    CU(cudaMemset(n->loss4_d, 0, 16));
     std::vector<float> m(P);
     uint64_t rng = n->seed;
     const int E = (int)n->enc_width;
@@ -374,6 +380,7 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.ema_debias_new = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)h->step));
     a.apply = apply;
     a.timeline = h->timeline;
+    a.perm_n = 0; a.perm_seed = 0; a.perm_base = 0;
     a.dp_world = 1; a.dp_rank = 0; a.dp_step = h->step; a.x_stride = h->x_stride;
     if (apply && h->dp_world > 1) {
         a.dp_world = (uint32_t)h->dp_world; a.dp_rank = (uint32_t)h->dp_rank;
@@ -505,6 +512,108 @@ int nrc_b200_train_dp(nrc_b200_handle h, const float* q, const float* t, uint32_
         CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));
         *loss_h = *h->loss_pinned;
+    }
+    return NRC_B200_OK;
+}
+
+// ---------------------------------------------------------------- NEXT rows: the per-frame sequence around the network
+int nrc_b200_accumulate_render_radiance(const float* radiance_d, const float* throughput_d, float* output_rgba_d,
+                                        uint32_t n_pixels, int render_mode, uint32_t iteration_index, void* cu_stream) {
+    if (n_pixels && (!radiance_d || !throughput_d || !output_rgba_d)) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    CU(launch_accumulate(radiance_d, throughput_d, output_rgba_d, n_pixels, render_mode, iteration_index, (cudaStream_t)cu_stream));
+    return NRC_B200_OK;
+}
+int nrc_b200_propagate_train_radiance(const nrc_b200_suffix_end_vertex* end_vertices_d, const float* end_radiance_d,
+                                      const nrc_b200_training_record* records_d, float* targets_d, uint32_t n_tiles,
+                                      void* cu_stream) {
+    if (n_tiles && (!end_vertices_d || !end_radiance_d || !records_d || !targets_d)) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    static_assert(sizeof(nrc_b200_training_record) == 28 && sizeof(nrc_b200_suffix_end_vertex) == 16, "record layouts");
+    CU(launch_propagate(end_vertices_d, end_radiance_d, records_d, targets_d, n_tiles, (cudaStream_t)cu_stream));
+    return NRC_B200_OK;
+}
+uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed) { return permute16(i & 0xFFFFu, seed); }
+int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
+                                int num_records, uint32_t seed, void* cu_stream) {
+    if (!q_src_d || !t_src_d || !q_dst_d || !t_dst_d) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    const int n = std::min(num_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
+    if (n <= 0) return NRC_B200_OK;        // nrc_helpers.cu:238: nothing to do
+    CU(launch_permute(q_src_d, t_src_d, q_dst_d, t_dst_d, (uint32_t)n, seed, (cudaStream_t)cu_stream));
+    return NRC_B200_OK;
+}
+void nrc_b200_adjust_tile_size(int tile_x, int tile_y, int num_train_records, int* new_x, int* new_y) {
+    // Device::adjustTileSize, Device.cpp:818-828
+    const float ratio = (float)(num_train_records * 1.25f) / (float)(NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
+    const float r = sqrtf(ratio);
+    if (new_x) *new_x = std::max((int)(tile_x * r + 0.5f), 2);
+    if (new_y) *new_y = std::max((int)(tile_y * r + 0.5f), 2);
+}
+
+static int train_shuffled_impl(Net* h, const float* q, const float* t, uint32_t n, uint32_t seed, uint32_t batch, float* loss_slot) {
+    h->step += 1;
+    h->barrier_total += NRC_B200_BATCH_SIZE / 128;
+    TrainArgs a = train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1);
+    a.perm_n = n; a.perm_seed = seed; a.perm_base = batch * NRC_B200_BATCH_SIZE;
+    if (loss_slot) a.loss_out = loss_slot;
+    CU(launch_train_step(h->encoding, a, h->gm, h->stream));
+    h->launches += 1;
+    return NRC_B200_OK;
+}
+// permute_train_data + Network::train on batch `batch_index` in one launch: the training kernel's loader gathers
+// src[permutation(d) % num_records] itself.
+int nrc_b200_train_shuffled(nrc_b200_handle h, const float* q_src_d, const float* t_src_d, int num_records, uint32_t seed,
+                            uint32_t batch_index, void* cu_stream, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q_src_d || !t_src_d) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    if (batch_index >= NRC_B200_NUM_BATCHES) return fail(NRC_B200_ERR_INVALID, "batch_index must be < 4");
+    const int n = std::min(num_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
+    if (n <= 0) return NRC_B200_OK;
+    int rc = train_shuffled_impl(h, q_src_d, t_src_d, (uint32_t)n, seed, batch_index, nullptr);
+    if (rc != NRC_B200_OK) return rc;
+    if (loss_h) {
+        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        *loss_h = *h->loss_pinned;
+    }
+    return NRC_B200_OK;
+}
+
+// The NRC part of Device::render (Device.cpp:2495-2515) in one call: infer -> accumulate -> propagate -> (fused shuffle) ->
+// 4 x train.  No host synchronisation unless stat != NULL (then one read-back of the four losses at the end; the
+// reference synchronises after every training step).
+int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream, nrc_b200_training_stat* stat) {
+    if (!h || !f) return fail(NRC_B200_ERR_INVALID, "null argument");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    const bool skip_render_cache = f->render_mode == 1 || f->render_mode == 3;   // NoCache, CacheFirstVertex
+    const float* q = f->queries_d;
+    float* r = f->results_d;
+    uint32_t n = f->num_pixels + f->num_tiles;
+    if (skip_render_cache) { q += (size_t)f->num_pixels * 15; r += (size_t)f->num_pixels * 3; n = f->num_tiles; }
+    int rc = nrc_b200_infer(h, q, r, n, nullptr);                                  // nrcInferRadiance
+    if (rc != NRC_B200_OK) return rc;
+    if (!skip_render_cache && f->throughput_d && f->output_rgba_d) {               // nrcAccumulateRadiance
+        CU(launch_accumulate(f->results_d, f->throughput_d, f->output_rgba_d, f->num_pixels, f->render_mode, f->iteration_index, h->stream));
+        h->launches += 1;
+    }
+    const int n_rec = std::min(f->num_train_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
+    if (stat) { stat->loss = 0.0f; stat->num_train_records = n_rec; }
+    if (n_rec > 0) {
+        if (f->end_vertices_d && f->records_d && f->num_tiles) {                   // nrcPropagateRadiance
+            CU(launch_propagate(f->end_vertices_d, f->results_d + (size_t)f->num_pixels * 3, f->records_d, f->train_targets_d,
+                                f->num_tiles, h->stream));
+            h->launches += 1;
+        }
+        for (uint32_t b = 0; b < NRC_B200_NUM_BATCHES; ++b) {                       // nrcShuffleTrainingData + nrcTrainRadiance
+            rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
+            if (rc != NRC_B200_OK) return rc;
+        }
+        if (stat) {
+            CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 16, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            stat->loss = (h->loss_pinned[0] + h->loss_pinned[1] + h->loss_pinned[2] + h->loss_pinned[3]) * (1.0f / NRC_B200_NUM_BATCHES);
+        }
     }
     return NRC_B200_OK;
 }

@@ -41,6 +41,9 @@ struct TrainArgs {
     // the receiver; grid part: floats + fence + per-slice flag.
     //   xbuf[r]  : rank r's buffer  float[2 parities][dp_world][x_stride]   (xbuf[dp_rank] is local memory)
     //   xflag[r] : rank r's flags   u32  [2 parities][dp_world][128 slices] (value = step number)
+    // Fused shuffle (perm_n > 0): sample d = perm_base + tile*128 + row reads record permute16(d, perm_seed) % perm_n
+    // of `in` / `targets` (the reference's permute_train_data, nrc_helpers.cu:226-249, without the 4.7 MB copy).
+    uint32_t perm_n, perm_seed, perm_base;
     uint32_t dp_world, dp_rank, dp_step, x_stride;
     float* xbuf[8];
     uint32_t* xflag[8];
@@ -53,5 +56,13 @@ cudaError_t launch_adam_ema(const TrainArgs& a, cudaStream_t stream);
 // Rebuilds the UMMA shared-memory image of the fp16 training weights (after a host upload).
 cudaError_t launch_make_image(const __half* params, __half* params_img, uint32_t enc_width, uint32_t n_mlp,
                               cudaStream_t stream);
+
+// nrc_frame.cu -- the helper kernels either side of the network in the per-frame sequence
+cudaError_t launch_accumulate(const float* radiance, const float* throughput, float* out4, uint32_t n_pixels, int mode,
+                              uint32_t iteration_index, cudaStream_t stream);
+cudaError_t launch_propagate(const void* end_vertices, const float* end_radiance, const void* records, float* targets,
+                             uint32_t n_tiles, cudaStream_t stream);
+cudaError_t launch_permute(const float* q_src, const float* t_src, float* q_dst, float* t_dst, uint32_t num_records,
+                           uint32_t seed, cudaStream_t stream);
 
 }  // namespace nrcb

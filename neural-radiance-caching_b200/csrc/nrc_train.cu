@@ -21,6 +21,7 @@
 #include <cuda_fp16.h>
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
+#include "nrc_frame.cuh"
 
 namespace nrcb {
 
@@ -211,7 +212,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t tile = blockIdx.x;
     const uint32_t n_tiles = gridDim.x;
-    const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0;
+    const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0 && a.perm_n == 0;   // bulk copy needs a contiguous tile
     auto stamp = [&](int slot) { if (a.timeline && tid == 0) a.timeline[tile * 8 + slot] = clock64(); };
     stamp(0);
 
@@ -290,6 +291,8 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         auto wait_mma = [&]() { mbar_wait(d_ready, ph); ph ^= 1; tc_fence_after(); };
         auto signal = [&]() { fence_proxy_async_smem(); tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(a_ready); };
 
+        // source record of this sample: contiguous, or gathered through the per-frame permutation (fused shuffle)
+        const uint32_t src_row = a.perm_n ? permute16(a.perm_base + tile * kTT + row, a.perm_seed) % a.perm_n : tile * kTT + row;
         float q[15];
         if (in_aligned) {
             mbar_wait(in_full, 0);
@@ -298,12 +301,12 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
         } else {
 #pragma unroll
-            for (int i = 0; i < 15; ++i) q[i] = __ldg(a.in + ((size_t)tile * kTT + row) * 15 + i);
+            for (int i = 0; i < 15; ++i) q[i] = __ldg(a.in + (size_t)src_row * 15 + i);
         }
         float tg[3] = {0.0f, 0.0f, 0.0f};
         if (hf == 0) {
 #pragma unroll
-            for (int c = 0; c < 3; ++c) tg[c] = __ldg(a.targets + ((size_t)tile * kTT + row) * 3 + c);
+            for (int c = 0; c < 3; ++c) tg[c] = __ldg(a.targets + (size_t)src_row * 3 + c);
         }
         {
             uint32_t e[E / 4];

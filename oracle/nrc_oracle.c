@@ -469,3 +469,70 @@ void nrc_oracle_state_init(nrc_oracle_state* st, uint64_t seed) {
     nrc_oracle_state_set_master(st, m, 1);
     free(m);
 }
+
+/* ---------------------------------------------------------------- NEXT rows (frame helpers) */
+/* nrc/shaders/nrc_helpers.cu:77-129 */
+void nrc_oracle_accumulate(const float* radiance, const float* throughput, float* out4, uint32_t n, int mode,
+                           uint32_t iteration_index) {
+    const float acc_weight = 1.0f / (float)(iteration_index + 1);
+    for (uint32_t i = 0; i < n; ++i) {
+        const float* r = radiance + 3 * (size_t)i; const float* t = throughput + 3 * (size_t)i; float* o = out4 + 4 * (size_t)i;
+        switch (mode) {
+            case 0: for (int c = 0; c < 3; ++c) o[c] = fmaf(t[c] * r[c], acc_weight, o[c]); o[3] = 1.0f; break;   /* Full */
+            case 2: for (int c = 0; c < 3; ++c) o[c] = r[c] * t[c]; o[3] = 1.0f; break;                          /* CacheOnly */
+            case 4: for (int c = 0; c < 3; ++c) o[c] = r[c]; o[3] = 1.0f; break;
+            case 5: for (int c = 0; c < 3; ++c) o[c] = t[c]; o[3] = 1.0f; break;
+            default: break;                                                                                       /* NoCache, CacheFirstVertex */
+        }
+    }
+}
+/* nrc/shaders/nrc_helpers.cu:131-224 (USE_REFLECTANCE_FACTORING = 0, config.h:118) */
+void nrc_oracle_propagate(const void* end_vertices, const float* end_radiance, const void* records, float* targets,
+                          uint32_t n_tiles) {
+    const int32_t* ev = (const int32_t*)end_vertices;
+    const int32_t* rec = (const int32_t*)records;
+    for (uint32_t tile = 0; tile < n_tiles; ++tile) {
+        float mask; memcpy(&mask, &ev[4 * tile + 1], 4);
+        float last[3];
+        for (int c = 0; c < 3; ++c) last[c] = end_radiance[3 * (size_t)tile + c] * mask;
+        int i = ev[4 * tile];
+        while (i >= 0) {
+            const int32_t* r = rec + 7 * (size_t)i;
+            for (int c = 0; c < 3; ++c) {
+                float lt; memcpy(&lt, &r[1 + c], 4);
+                last[c] = fmaf(lt, last[c], targets[3 * (size_t)i + c]);
+                targets[3 * (size_t)i + c] = last[c];
+            }
+            i = r[0];
+        }
+    }
+}
+static uint32_t feistel_round(uint32_t x, uint32_t key) {
+    x = (x + key) * 0x9E3779B1u; x ^= x >> 15; x *= 0x85EBCA77u; x ^= x >> 13;
+    return x & 0xFFu;
+}
+uint32_t nrc_oracle_permutation(uint32_t i, uint32_t seed) {
+    uint32_t l = (i >> 8) & 0xFFu, r = i & 0xFFu;
+    for (uint32_t k = 0; k < 4; ++k) {
+        const uint32_t t = l ^ feistel_round(r, seed * 4u + k + 0x632BE5ABu * (k + 1u));
+        l = r; r = t;
+    }
+    return (l << 8) | r;
+}
+/* nrc/shaders/nrc_helpers.cu:226-249 */
+void nrc_oracle_permute(const float* q_src, const float* t_src, float* q_dst, float* t_dst, int num_records, uint32_t seed) {
+    const int n = num_records < 65536 ? num_records : 65536;
+    if (n <= 0) return;
+    for (uint32_t d = 0; d < 65536; ++d) {
+        const uint32_t s = nrc_oracle_permutation(d, seed) % (uint32_t)n;
+        memcpy(q_dst + 15 * (size_t)d, q_src + 15 * (size_t)s, 60);
+        memcpy(t_dst + 3 * (size_t)d, t_src + 3 * (size_t)s, 12);
+    }
+}
+/* nrc/src/Device.cpp:818-828 */
+void nrc_oracle_adjust_tile_size(int tx, int ty, int num_records, int* nx, int* ny) {
+    const float ratio = (float)(num_records * 1.25f) / (float)65536;
+    const float r = sqrtf(ratio);
+    int x = (int)(tx * r + 0.5f), y = (int)(ty * r + 0.5f);
+    *nx = x > 2 ? x : 2; *ny = y > 2 ? y : 2;
+}

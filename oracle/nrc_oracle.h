@@ -76,6 +76,25 @@ float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* t
                            float* grad_accum, int nthreads);
 void nrc_oracle_apply_grads(nrc_oracle_state* st, const float* grad_accum);
 
+/* ---- NEXT rows: CPU restatements of the helper kernels around the network.
+ * PARITY: these reference kernels live in the OptiX module (nrc/shaders/nrc_helpers.cu reads launch state from the
+ * `sysData` constant and needs optix.h / system_data.h), so they cannot be compiled without the OptiX SDK:
+ * "parity unpinned" by reference outputs for these rows; they are restated from the source.  Multiply-adds are written
+ * as fmaf because nvcc (default -fmad=true) contracts `a += b * c` in the reference kernels. */
+/* accumulate_render_radiance, nrc_helpers.cu:77-129; out4 = float4[n] */
+void nrc_oracle_accumulate(const float* radiance, const float* throughput, float* out4, uint32_t n, int mode,
+                           uint32_t iteration_index);
+/* propagate_train_radiance, nrc_helpers.cu:131-224; end_vertices = {int start; float mask; int; int}[n_tiles],
+ * records = {int propTo; float lt[3]; int; int; int}[<=65536] */
+void nrc_oracle_propagate(const void* end_vertices, const float* end_radiance, const void* records, float* targets,
+                          uint32_t n_tiles);
+/* The keyed 16-bit bijection that replaces cuRAND keys + CUB sort (NRCUtil.cu:20-35); must equal nrc_b200_permutation. */
+uint32_t nrc_oracle_permutation(uint32_t i, uint32_t seed);
+/* permute_train_data, nrc_helpers.cu:226-249 */
+void nrc_oracle_permute(const float* q_src, const float* t_src, float* q_dst, float* t_dst, int num_records, uint32_t seed);
+/* Device::adjustTileSize, Device.cpp:818-828 */
+void nrc_oracle_adjust_tile_size(int tx, int ty, int num_records, int* nx, int* ny);
+
 /* Pieces exposed for unit tests. */
 float nrc_oracle_quartic_cdf(float x, float inv_radius);
 void nrc_oracle_oneblob4_aos(float x, float out[4]);

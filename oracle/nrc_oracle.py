@@ -62,6 +62,12 @@ def lib():
         L.nrc_oracle_triwave.restype = f32
         L.nrc_oracle_grid_index.argtypes = [u32] * 5
         L.nrc_oracle_grid_index.restype = u32
+        L.nrc_oracle_accumulate.argtypes = [vp, vp, vp, u32, i32, u32]
+        L.nrc_oracle_propagate.argtypes = [vp, vp, vp, vp, u32]
+        L.nrc_oracle_permutation.argtypes = [u32, u32]
+        L.nrc_oracle_permutation.restype = u32
+        L.nrc_oracle_permute.argtypes = [vp, vp, vp, vp, i32, u32]
+        L.nrc_oracle_adjust_tile_size.argtypes = [i32, i32, i32, ctypes.POINTER(i32), ctypes.POINTER(i32)]
         _lib = L
     return _lib
 
@@ -150,3 +156,42 @@ class Trainer:
 
     def infer(self, queries, use_ema=True, acc_mode=0, nthreads=None):
         return infer(self.spec, self.ema if use_ema else self.params, queries, acc_mode, nthreads)
+
+
+# ---- NEXT rows (frame helpers) ---------------------------------------------------------------------------------
+RECORD_DTYPE = np.dtype([("propTo", np.int32), ("localThroughput", np.float32, 3), ("pixelIndex", np.int32),
+                         ("tileIndex", np.int32), ("propLength", np.int32)])                       # nrc::TrainingRecord
+END_VERTEX_DTYPE = np.dtype([("startTrainRecord", np.int32), ("radianceMask", np.float32), ("pixelIndex", np.int32),
+                             ("tileIndex", np.int32)])                                               # TrainingSuffixEndVertex
+
+
+def accumulate(radiance, throughput, out4, mode, iteration_index):
+    r = np.ascontiguousarray(radiance, np.float32); t = np.ascontiguousarray(throughput, np.float32)
+    o = np.ascontiguousarray(out4, np.float32).copy()
+    lib().nrc_oracle_accumulate(r.ctypes.data, t.ctypes.data, o.ctypes.data, r.shape[0], mode, iteration_index)
+    return o
+
+
+def propagate(end_vertices, end_radiance, records, targets):
+    ev = np.ascontiguousarray(end_vertices); rec = np.ascontiguousarray(records)
+    assert ev.dtype == END_VERTEX_DTYPE and rec.dtype == RECORD_DTYPE
+    er = np.ascontiguousarray(end_radiance, np.float32); t = np.ascontiguousarray(targets, np.float32).copy()
+    lib().nrc_oracle_propagate(ev.ctypes.data, er.ctypes.data, rec.ctypes.data, t.ctypes.data, ev.shape[0])
+    return t
+
+
+def permutation(i, seed):
+    return lib().nrc_oracle_permutation(int(i), int(seed))
+
+
+def permute(q_src, t_src, num_records, seed):
+    q = np.ascontiguousarray(q_src, np.float32); t = np.ascontiguousarray(t_src, np.float32)
+    qd = np.zeros((65536, 15), np.float32); td = np.zeros((65536, 3), np.float32)
+    lib().nrc_oracle_permute(q.ctypes.data, t.ctypes.data, qd.ctypes.data, td.ctypes.data, int(num_records), int(seed))
+    return qd, td
+
+
+def adjust_tile_size(tx, ty, num_records):
+    x, y = ctypes.c_int(), ctypes.c_int()
+    lib().nrc_oracle_adjust_tile_size(tx, ty, num_records, ctypes.byref(x), ctypes.byref(y))
+    return x.value, y.value
