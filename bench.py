@@ -317,6 +317,34 @@ def run_ours(args, enc):
            "h2d_bytes_per_step": nq * 60 + n_train * 72, "d2h_bytes_per_step": nq * 12 + 4,
            "timing": "host wall clock between device synchronisations, max over ranks"}
 
+    # ---- the whole NRC sequence of Device::render through the frame driver (NEXT rows included): infer -> accumulate ->
+    #      propagate -> fused shuffle -> 4 x train, device-resident buffers, CUDA events
+    frame_ms = None
+    if world == 1:
+        n_px, n_tiles = 2560 * 1440, FRAME_QUERIES - 2560 * 1440
+        if nq == FRAME_QUERIES:
+            rng = np.random.default_rng(5)
+            thr_d = torch.from_numpy(rng.uniform(0, 1, (n_px, 3)).astype(np.float32)).cuda()
+            out4_d = torch.zeros((n_px, 4), device="cuda")
+            ev_np, rec_np, used = synth.training_chains(n_tiles)
+            ev_d, rec_d = torch.from_numpy(ev_np).cuda(), torch.from_numpy(rec_np).cuda()
+            tgt_work = tt_d.clone()
+            fr = pkg.Frame(q_d.data_ptr(), out_d.data_ptr(), n_px, n_tiles, thr_d.data_ptr(), out4_d.data_ptr(), pkg.RENDER_FULL, 0,
+                           ev_d.data_ptr(), rec_d.data_ptr(), tq_d.data_ptr(), tgt_work.data_ptr(), used, 0)
+            for i in range(3):
+                net.update(fr, sp)
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n_fr = max(10, min(args.steps, 100))
+            f0.record(stream)
+            for i in range(n_fr):
+                fr.iteration_index, fr.shuffle_seed = i, i
+                tgt_work.copy_(tt_d)              # Device::render zeroes / refills the targets every frame (Device.cpp:2471-2476)
+                net.update(fr, sp)
+            f1.record(stream)
+            torch.cuda.synchronize()
+            frame_ms = f0.elapsed_time(f1) / n_fr
+
     # ---- roofline of the dominant kernel (fused query kernel), live CUDA-event duration per launch
     peaks = {}
     try:
@@ -342,7 +370,7 @@ def run_ours(args, enc):
             "queries_per_s": world * nq / (t_inf_ms * 1e-3),
             "train_samples_per_s": world * n_train / max((ms_step - t_inf_ms) * 1e-3, 1e-9),
             "ms_infer": t_inf_ms, "ms_train_4_steps": ms_step - t_inf_ms,
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
+            "frame_driver_ms": frame_ms, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
     net.destroy()
     return line, rank, world
 
@@ -360,7 +388,9 @@ def time_reference_gpu(enc, nq):
     return json.loads(r.stdout.strip().splitlines()[-1])
 
 
-TRAFFIC_BYTES = {}   # (encoding, queries) -> dram bytes per launch from an `ncu --set full` capture (profiles/)
+# (encoding, queries) -> dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the query kernel, from the
+# `ncu --set full` captures summarised in profiles/r01_infer_{frequency,hash}_ncu.txt (algorithmic: 72 B/query = 269.6 MB)
+TRAFFIC_BYTES = {(0, FRAME_QUERIES): 224737280 + 33306112, (1, FRAME_QUERIES): 226391808 + 35820032}
 
 
 def main():

@@ -591,12 +591,14 @@ int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream,
     float* r = f->results_d;
     uint32_t n = f->num_pixels + f->num_tiles;
     if (skip_render_cache) { q += (size_t)f->num_pixels * 15; r += (size_t)f->num_pixels * 3; n = f->num_tiles; }
-    int rc = nrc_b200_infer(h, q, r, n, nullptr);                                  // nrcInferRadiance
-    if (rc != NRC_B200_OK) return rc;
-    if (!skip_render_cache && f->throughput_d && f->output_rgba_d) {               // nrcAccumulateRadiance
-        CU(launch_accumulate(f->results_d, f->throughput_d, f->output_rgba_d, f->num_pixels, f->render_mode, f->iteration_index, h->stream));
-        h->launches += 1;
-    }
+    if (n && (!q || !r)) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    // nrcInferRadiance + nrcAccumulateRadiance in ONE launch: the query kernel's epilogue accumulates the pixel part
+    AccumArgs acc{nullptr, nullptr, 0, 0, 0.0f};
+    if (!skip_render_cache && f->throughput_d && f->output_rgba_d)
+        acc = AccumArgs{f->throughput_d, reinterpret_cast<float4*>(f->output_rgba_d), f->num_pixels, f->render_mode,
+                        1.0f / (float)(f->iteration_index + 1)};
+    CU(launch_infer(h->encoding, q, r, n, h->ema, h->gm, h->num_sms, h->stream, &acc));
+    h->launches += 1;
     const int n_rec = std::min(f->num_train_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
     if (stat) { stat->loss = 0.0f; stat->num_train_records = n_rec; }
     if (n_rec > 0) {
@@ -606,7 +608,7 @@ int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream,
             h->launches += 1;
         }
         for (uint32_t b = 0; b < NRC_B200_NUM_BATCHES; ++b) {                       // nrcShuffleTrainingData + nrcTrainRadiance
-            rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
+            int rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
             if (rc != NRC_B200_OK) return rc;
         }
         if (stat) {

@@ -34,7 +34,9 @@ struct InferSmem {
     static constexpr int kOut = kTile * 3 * 4;        // 1536 B of results per group
     static constexpr int kInOff = kWeights;
     static constexpr int kOutOff = kInOff + kGroups * kStage;
-    static constexpr int kBarOff = kOutOff + kGroups * kOut;
+    static constexpr int kAcc = kTile * 12 + kTile * 16;   // fused accumulation: throughput (1536 B) + output (2048 B) of a tile
+    static constexpr int kAccOff = kOutOff + kGroups * kOut;           // [kGroups][2 parities][kAcc]
+    static constexpr int kBarOff = kAccOff + kGroups * 2 * kAcc;
     static constexpr int kTotal = kBarOff + 256;
 };
 
@@ -101,7 +103,7 @@ __device__ __forceinline__ void mma_issuer(uint8_t* smem, uint32_t tmem_base, ui
 template <int ENC>  // 0 = Frequency (E = 80), 1 = Hash (E = 64)
 __global__ void __launch_bounds__(kThreads, 1)
 nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t n, const __half* __restrict__ params,
-                 GridMeta gm) {
+                 GridMeta gm, AccumArgs acc) {
     constexpr int E = ENC == 0 ? 80 : 64;
     using L = InferSmem<E>;
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -152,11 +154,25 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         const bool in_bulk_ok = (reinterpret_cast<uintptr_t>(in) & 15) == 0;
         const bool out_vec_ok = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
 
-        auto load_tile = [&](uint32_t t) {  // called by all 128 threads of the group, after a group_sync
+        uint8_t* s_acc = smem + L::kAccOff + g * 2 * L::kAcc;
+        const bool acc_bulk_ok = acc.out != nullptr && (reinterpret_cast<uintptr_t>(acc.throughput) & 15) == 0 &&
+                                 (reinterpret_cast<uintptr_t>(acc.out) & 15) == 0;
+        // tiles whose 128 queries are all pixels prefetch throughput + output rows with the same mbarrier as the input
+        auto acc_staged = [&](uint32_t t) { return acc_bulk_ok && in_bulk_ok && (t + 1) * kTile <= acc.n && (t + 1) * kTile <= n; };
+
+        auto load_tile = [&](uint32_t t, uint32_t par) {  // called by all 128 threads of the group, after a group_sync
             const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
             const float* src = in + (size_t)t * kTile * 15;
             if (in_bulk_ok && rows == kTile) {
-                if (gtid == 0) { mbar_arrive_expect_tx(&in_full[g], L::kStage); bulk_g2s(s_in, src, L::kStage, &in_full[g]); }
+                if (gtid == 0) {
+                    const bool st = acc_staged(t);
+                    mbar_arrive_expect_tx(&in_full[g], L::kStage + (st ? L::kAcc : 0));
+                    bulk_g2s(s_in, src, L::kStage, &in_full[g]);
+                    if (st) {
+                        bulk_g2s(s_acc + par * L::kAcc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &in_full[g]);
+                        bulk_g2s(s_acc + par * L::kAcc + kTile * 12, acc.out + (size_t)t * kTile, kTile * 16, &in_full[g]);
+                    }
+                }
             } else {  // ragged tail / unaligned caller buffer: plain loads, zero-fill the missing rows
                 for (uint32_t i = gtid; i < kTile * 15; i += 128) s_in[i] = i < rows * 15 ? __ldg(src + i) : 0.0f;
                 group_sync(g);
@@ -165,8 +181,8 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         };
 
         uint32_t t = blockIdx.x * kGroups + g;
-        uint32_t ph_in = 0, ph_d = 0;
-        if (t < n_tiles) load_tile(t);
+        uint32_t ph_in = 0, ph_d = 0, par = 0;
+        if (t < n_tiles) load_tile(t, 0);
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
             float q[15];
@@ -174,7 +190,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
             fence_proxy_async_smem();                        // order these generic reads before the next bulk write
             group_sync(g);                                   // everyone holds its query: the stage is free
-            if (t + tile_stride < n_tiles) load_tile(t + tile_stride);
+            if (t + tile_stride < n_tiles) load_tile(t + tile_stride, par ^ 1);
 
             // ---- encode -> A operand of the input layer
             {
@@ -226,6 +242,33 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             }
             // D is drained; the next tile's first arrive (after its encode) re-arms the MMA warp.
             const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
+            // Fused accumulate_render_radiance (nrc_helpers.cu:77-129) for the pixel queries: the radiance is still in
+            // registers, so the separate pass (re-read 12 B radiance, 12 B throughput, 16 B output per pixel) disappears.
+            if (acc.out != nullptr) {
+                const uint32_t px = t * kTile + row;
+                if (px < acc.n && row < rows) {
+                    float t0, t1, t2;
+                    float4 d;
+                    if (acc_staged(t)) {
+                        const float* st = reinterpret_cast<const float*>(s_acc + par * L::kAcc);
+                        t0 = st[3 * row]; t1 = st[3 * row + 1]; t2 = st[3 * row + 2];
+                        d = reinterpret_cast<const float4*>(s_acc + par * L::kAcc + kTile * 12)[row];
+                    } else {
+                        t0 = __ldg(acc.throughput + 3 * (size_t)px); t1 = __ldg(acc.throughput + 3 * (size_t)px + 1);
+                        t2 = __ldg(acc.throughput + 3 * (size_t)px + 2);
+                        d = acc.mode == 0 ? acc.out[px] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    }
+                    float4* o = acc.out + px;
+                    switch (acc.mode) {
+                        case 0: *o = make_float4(fmaf(t0 * y[0], acc.weight, d.x), fmaf(t1 * y[1], acc.weight, d.y), fmaf(t2 * y[2], acc.weight, d.z), 1.0f); break;
+                        case 2: *o = make_float4(y[0] * t0, y[1] * t1, y[2] * t2, 1.0f); break;
+                        case 4: *o = make_float4(y[0], y[1], y[2], 1.0f); break;
+                        case 5: *o = make_float4(t0, t1, t2, 1.0f); break;
+                        default: break;
+                    }
+                }
+            }
+            par ^= 1;
             float* dst = out + (size_t)t * kTile * 3;
             if (out_vec_ok && rows == kTile) {
                 s_out[row * 3 + 0] = y[0]; s_out[row * 3 + 1] = y[1]; s_out[row * 3 + 2] = y[2];
@@ -243,7 +286,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
 
 template <int ENC>
 static cudaError_t launch_infer_t(const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
-                                  int num_sms, cudaStream_t stream) {
+                                  int num_sms, cudaStream_t stream, const AccumArgs& acc) {
     using L = InferSmem<ENC == 0 ? 80 : 64>;
     static bool configured[2] = {false, false};
     if (!configured[ENC]) {
@@ -253,15 +296,16 @@ static cudaError_t launch_infer_t(const float* in, float* out, uint32_t n, const
     }
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
     const uint32_t grid = min((uint32_t)num_sms, (n_tiles + kGroups - 1) / kGroups);
-    nrc_infer_kernel<ENC><<<grid, kThreads, L::kTotal, stream>>>(in, out, n, params, gm);
+    nrc_infer_kernel<ENC><<<grid, kThreads, L::kTotal, stream>>>(in, out, n, params, gm, acc);
     return cudaGetLastError();
 }
 
 cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
-                         int num_sms, cudaStream_t stream) {
+                         int num_sms, cudaStream_t stream, const AccumArgs* acc) {
     if (n == 0) return cudaSuccess;
-    return encoding == 0 ? launch_infer_t<0>(in, out, n, params, gm, num_sms, stream)
-                         : launch_infer_t<1>(in, out, n, params, gm, num_sms, stream);
+    const AccumArgs a = acc ? *acc : AccumArgs{nullptr, nullptr, 0, 0, 0.0f};
+    return encoding == 0 ? launch_infer_t<0>(in, out, n, params, gm, num_sms, stream, a)
+                         : launch_infer_t<1>(in, out, n, params, gm, num_sms, stream, a);
 }
 
 }  // namespace nrcb

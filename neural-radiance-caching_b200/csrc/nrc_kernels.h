@@ -8,9 +8,17 @@ namespace nrcb {
 
 struct GridMeta;
 
-// nrc_infer.cu -- fused query kernel (encodings + 6-matrix MLP), EMA weights.
+// nrc_infer.cu -- fused query kernel (encodings + 6-matrix MLP), EMA weights.  Optional fused epilogue: the first
+// acc->n queries are pixels whose radiance is accumulated into the output image (accumulate_render_radiance).
+struct AccumArgs {
+    const float* throughput;   // float3[n]
+    float4* out;               // float4[n], nullptr = no accumulation
+    uint32_t n;
+    int mode;                  // nrc::RenderMode
+    float weight;              // 1 / (iterationIndex + 1)
+};
 cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
-                         int num_sms, cudaStream_t stream);
+                         int num_sms, cudaStream_t stream, const AccumArgs* acc = nullptr);
 
 // nrc_train.cu -- ONE cooperative kernel per optimizer step:
 //   phase 1  per 128-sample tile: encodings, forward, loss, backward, per-tile weight gradients (tcgen05)

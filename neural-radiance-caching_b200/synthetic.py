@@ -69,3 +69,30 @@ def radiance_targets(q, seed=1337):
     base = (0.5 + 0.5 * np.cos(40.0 * q[:, 0]) * np.cos(40.0 * q[:, 1])) * (1.0 + q[:, 5] / np.pi)
     t = q[:, 9:12] * base[:, None] * (1.0 + 0.01 * rng.standard_normal((q.shape[0], 1)))
     return np.ascontiguousarray(np.maximum(t, 0.0).astype(np.float32))
+
+
+def training_chains(n_tiles, n_records=65536, seed=1337, max_len=2):
+    """Synthetic stand-in for what the path tracer leaves for radiance propagation (nrc/shaders/hit.cu): one
+    nrc::TrainingSuffixEndVertex per tile pointing at a chain of 0..max_len nrc::TrainingRecord's linked by propTo.
+    Returns (end_vertices int32[n_tiles, 4], records int32[n_records, 7], records_used); float fields are stored as
+    their bit patterns (layouts: include/nrc_b200.h)."""
+    rng = np.random.Generator(np.random.Philox(seed + 29))
+    length = rng.integers(0, max_len + 1, n_tiles)
+    start = np.concatenate([[0], np.cumsum(length)[:-1]])
+    length = np.where(start + length <= n_records, length, 0)
+    used = int((start + length).max()) if n_tiles else 0
+    rec = np.zeros((n_records, 7), dtype=np.int32)
+    rec[:, 0] = -1
+    ids = np.arange(n_records)
+    owner = np.searchsorted(start + length, ids, side="right")          # tile owning record i (if i < used)
+    valid = (ids < used) & (owner < n_tiles)
+    last = np.zeros(n_records, dtype=bool)
+    last[valid] = ids[valid] == (start + length)[owner[valid]] - 1
+    rec[valid & ~last, 0] = ids[valid & ~last] + 1
+    rec[:, 1:4] = rng.uniform(0.0, 1.1, (n_records, 3)).astype(np.float32).view(np.int32)
+    rec[valid, 5] = owner[valid]
+    ev = np.zeros((n_tiles, 4), dtype=np.int32)
+    ev[:, 0] = np.where(length > 0, start, -1)
+    ev[:, 1] = (rng.random(n_tiles) > 1.0 / 16.0).astype(np.float32).view(np.int32)   # TRAIN_UNBIASED_RATIO = 1/16
+    ev[:, 3] = np.arange(n_tiles)
+    return ev, rec, used
