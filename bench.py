@@ -46,6 +46,9 @@ def parse_args():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--encoding", choices=["frequency", "hash"], default="frequency")
     ap.add_argument("--queries", type=int, default=FRAME_QUERIES, help="queries per update per GPU")
+    ap.add_argument("--query-order", choices=["frame", "random"], default="frame",
+                    help="frame: pixel-ordered primary hits of a camera in the Cornell box + incoherent tile tails (what a "
+                         "renderer hands over); random: independent random surface points (incoherent worst case)")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dp", choices=["fused", "nccl"], default="fused",
@@ -60,19 +63,26 @@ def workload_name(enc, nq):
             f"training samples, {'Frequency' if enc == 0 else 'Hash'} encoding, 5x64 ReLU MLP")
 
 
-def make_inputs(synth, nq, rank):
-    """Seeded Cornell-box-shaped queries (host, float32).  The generator is tiled from a 2^20 block to keep
-    start-up short; every 2^20 block is shifted by a different seed."""
-    blocks, left, b = [], nq, 0
-    while left > 0:
-        m = min(left, 1 << 20)
-        blocks.append(synth.cornell_queries(m, seed=1337 + 97 * rank + b))
-        left -= m
-        b += 1
-    q = np.concatenate(blocks, axis=0)
+def make_inputs(synth, nq, rank, order="frame"):
+    """Seeded Cornell-box queries (host, float32).  order == "frame": 2560-pixel-wide rows of primary hits in pixel order,
+    the last 320x180 (or 1/65 of a non-default count) being incoherent tile tails; "random": independent surface points,
+    tiled from 2^20-query blocks to keep start-up short."""
+    if order == "frame":
+        n_tail = 320 * 180 if nq == FRAME_QUERIES else nq // 65
+        rows = -(-(nq - n_tail) // 2560)
+        px = synth.cornell_frame(2560, rows, seed=1337 + 97 * rank)[:nq - n_tail]
+        q = np.concatenate([px, synth.cornell_queries(n_tail, seed=1342 + 97 * rank)], axis=0) if n_tail else px
+    else:
+        blocks, left, b = [], nq, 0
+        while left > 0:
+            m = min(left, 1 << 20)
+            blocks.append(synth.cornell_queries(m, seed=1337 + 97 * rank + b))
+            left -= m
+            b += 1
+        q = np.concatenate(blocks, axis=0)
     tq = synth.cornell_queries(NUM_BATCHES * BATCH_SIZE, seed=4242 + rank)
     tt = synth.radiance_targets(tq, seed=4242 + rank)
-    return q, tq, tt
+    return np.ascontiguousarray(q), tq, tt
 
 
 class ClockSampler(threading.Thread):
@@ -221,7 +231,7 @@ def run_ours(args, enc):
     n_train = NUM_BATCHES * BATCH_SIZE
 
     # ---- inputs: host (pinned) + device-resident copies
-    q_np, tq_np, tt_np = make_inputs(synth, nq, rank)
+    q_np, tq_np, tt_np = make_inputs(synth, nq, rank, args.query_order)
     q_h = torch.from_numpy(q_np).pin_memory()
     tq_h = torch.from_numpy(tq_np).pin_memory()
     tt_h = torch.from_numpy(tt_np).pin_memory()
@@ -366,6 +376,9 @@ def run_ours(args, enc):
             "data": "synthetic",
             "config": {"workload": workload_name(enc, nq), "queries_per_gpu": nq, "train_samples_per_gpu": n_train,
                        "parallelism": (f"dp{world} ({args.dp} all-reduce)") if world > 1 else "single",
+                       "query_order": ("pixel-ordered primary hits of a pinhole camera in the Cornell box + incoherent "
+                                       "tile tails" if args.query_order == "frame" else
+                                       "independent random surface points (incoherent worst case for the hash grid)"),
                        "l2": f"inputs larger than L2 ({nq * 60 / 1e6:.0f} MB of queries per step vs 126 MB L2)"},
             "queries_per_s": world * nq / (t_inf_ms * 1e-3),
             "train_samples_per_s": world * n_train / max((ms_step - t_inf_ms) * 1e-3, 1e-9),

@@ -56,6 +56,52 @@ def cornell_queries(n, seed=1337):
     return np.ascontiguousarray(q)
 
 
+def cornell_frame(width, height, seed=1337, n_tail=0):
+    """width*height x 15 float32 queries in PIXEL ORDER (row-major), the way Device::render leaves them in
+    radianceQueriesInference: one primary hit per pixel of a pinhole camera looking into the Cornell box through its
+    open face (camera on the +z axis, 1 jittered sample per pixel), followed by n_tail incoherent queries (the path
+    tails of the training tiles).  Neighbouring pixels hit neighbouring surface points, which is what makes the hash-grid
+    gathers of a real frame cache-friendly; cornell_queries() is the incoherent worst case."""
+    rng = np.random.Generator(np.random.Philox(seed + 3))
+    n = width * height
+    jx, jy = rng.random(n, dtype=np.float32), rng.random(n, dtype=np.float32)
+    px = (np.arange(n, dtype=np.int64) % width).astype(np.float32)
+    py = (np.arange(n, dtype=np.int64) // width).astype(np.float32)
+    u = ((px + jx) / width * 2.0 - 1.0).astype(np.float64) * 0.5
+    v = ((py + jy) / height * 2.0 - 1.0).astype(np.float64) * (0.5 * height / width)
+    d = np.stack([u, v, -np.ones(n)], axis=1)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o = np.array([0.0, 0.0, 30.0])
+    # nearest hit among the five walls x = +-10, y = +-10, z = -10 (the face z = +10 is open)
+    tbest = np.full(n, np.inf)
+    wall = np.zeros(n, dtype=np.int64)
+    for w, (a, sgn) in enumerate([(0, -1.0), (0, 1.0), (1, -1.0), (1, 1.0), (2, -1.0)]):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t = (sgn * 10.0 - o[a]) / d[:, a]
+        hit = o[None, :] + t[:, None] * d
+        ok = (t > 0) & np.all(np.abs(hit) <= 10.0 + 1e-9, axis=1) & (t < tbest)
+        tbest = np.where(ok, t, tbest)
+        wall = np.where(ok, w, wall)
+    pos = o[None, :] + tbest[:, None] * d
+    nrm = np.zeros((n, 3))
+    axis, sgn = np.array([0, 0, 1, 1, 2])[wall], np.array([-1.0, 1.0, -1.0, 1.0, -1.0])[wall]
+    nrm[np.arange(n), axis] = -sgn
+    q = np.empty((n, 15), dtype=np.float32)
+    q[:, 0:3] = pos * 0.005
+    q[:, 3], q[:, 4] = _sph(-d)
+    q[:, 5], q[:, 6] = _sph(nrm)
+    q[:, 7] = (0.3 + 0.05 * wall).astype(np.float32)            # per-material roughness
+    q[:, 8] = 0.5
+    diffuse = np.full((n, 3), 0.8)
+    diffuse[wall == 0] = (0.8, 0.1, 0.1)   # red wall
+    diffuse[wall == 1] = (0.1, 0.8, 0.1)   # green wall
+    q[:, 9:12] = diffuse
+    q[:, 12:15] = 0.0
+    if n_tail:
+        q = np.concatenate([q, cornell_queries(n_tail, seed=seed + 5)], axis=0)
+    return np.ascontiguousarray(q)
+
+
 def uniform_queries(n, seed=1337):
     """All 15 inputs ~ U[0,1): the one-blob encoding in its non-degenerate regime."""
     rng = np.random.Generator(np.random.Philox(seed + 7))
