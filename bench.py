@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--query-order", choices=["frame", "random"], default="frame",
                     help="frame: pixel-ordered primary hits of a camera in the Cornell box + incoherent tile tails (what a "
                          "renderer hands over); random: independent random surface points (incoherent worst case)")
+    ap.add_argument("--per-batch-launch", action="store_true",
+                    help="one nrc_b200_train launch per batch (the reference's call pattern) instead of nrc_b200_train_batches")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dp", choices=["fused", "nccl"], default="fused",
@@ -263,8 +265,11 @@ def run_ours(args, enc):
         net.infer(q_d, out_d, nq, sp)
         if step_idx is not None:
             ev_inf[step_idx][1].record(stream)
-        for b in range(NUM_BATCHES):
-            train_batch(b)
+        if world == 1 and not args.per_batch_launch:
+            net.train_batches(q_ptr_t, t_ptr_t, NUM_BATCHES, sp)     # Device::nrcTrainRadiance: 4 steps, one launch
+        else:
+            for b in range(NUM_BATCHES):
+                train_batch(b)
 
     def barrier():
         if world > 1:

@@ -115,6 +115,11 @@ int nrc_b200_accumulate_render_radiance(const float* radiance_d, const float* th
 int nrc_b200_propagate_train_radiance(const nrc_b200_suffix_end_vertex* end_vertices_d, const float* end_radiance_d,
                                       const nrc_b200_training_record* records_d, float* targets_d, uint32_t n_tiles,
                                       void* cu_stream);
+/* Device::nrcTrainRadiance (Device.cpp:1482-1513): n_batches (1..NRC_B200_NUM_BATCHES) consecutive Network::train calls on
+ * queries_d + b*16384*15 / targets_d + b*16384*3 as ONE launch (grid barriers between the steps instead of launch
+ * boundaries); bit-identical to the loop of nrc_b200_train calls.  loss_h (optional, blocks) = mean of the batch losses. */
+int nrc_b200_train_batches(nrc_b200_handle h, const float* queries_d, const float* targets_d, int n_batches,
+                           void* cu_stream, float* loss_h);
 /* generateRandomPermutationForTrain + permute_train_data (NRCUtil.cu:20-35, nrc_helpers.cu:226-249): dst[d] =
  * src[permutation(d, seed) % min(num_records, 65536)], d < 65536.  The permutation is a keyed 16-bit bijection
  * (nrc_b200_permutation) instead of cuRAND keys + a CUB radix sort. */

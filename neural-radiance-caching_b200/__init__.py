@@ -33,7 +33,7 @@ ABI_SYMBOLS = [
     "nrc_b200_n_params", "nrc_b200_get_params", "nrc_b200_set_params", "nrc_b200_load_master",
     "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline", "nrc_b200_dp_export", "nrc_b200_dp_connect", "nrc_b200_train_dp",
     "nrc_b200_accumulate_render_radiance", "nrc_b200_propagate_train_radiance", "nrc_b200_permutation",
-    "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_adjust_tile_size", "nrc_b200_update",
+    "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_train_batches", "nrc_b200_adjust_tile_size", "nrc_b200_update",
 ]
 
 
@@ -102,6 +102,7 @@ def lib():
         L.nrc_b200_permutation.restype = u32
         L.nrc_b200_permute_train_data.argtypes = [vp, vp, vp, vp, i32, u32, vp]
         L.nrc_b200_train_shuffled.argtypes = [vp, vp, vp, i32, u32, u32, vp, P(f32)]
+        L.nrc_b200_train_batches.argtypes = [vp, vp, vp, i32, vp, P(f32)]
         L.nrc_b200_adjust_tile_size.argtypes = [i32, i32, i32, P(i32), P(i32)]
         L.nrc_b200_adjust_tile_size.restype = None
         L.nrc_b200_update.argtypes = [vp, P(Frame), vp, P(TrainingStat)]
@@ -254,6 +255,13 @@ class Network:
         return loss.value if want_loss else None
 
     # ---- NEXT rows: the per-frame sequence around the network (Device::render) ------------------------------
+    def train_batches(self, queries_d, targets_d, n_batches, stream=None, want_loss=False):
+        """n_batches consecutive train() calls (Device::nrcTrainRadiance) as one launch; returns the mean loss if asked."""
+        loss = ctypes.c_float()
+        _check(lib().nrc_b200_train_batches(self._h, _ptr(queries_d), _ptr(targets_d), int(n_batches), _ptr(stream),
+                                            ctypes.byref(loss) if want_loss else None))
+        return loss.value if want_loss else None
+
     def train_shuffled(self, q_src_d, t_src_d, num_records, seed, batch_index, stream=None, want_loss=False):
         loss = ctypes.c_float()
         _check(lib().nrc_b200_train_shuffled(self._h, _ptr(q_src_d), _ptr(t_src_d), int(num_records), int(seed),

@@ -364,7 +364,9 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
 }
 
 // ---------------------------------------------------------------- training
-static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_local, uint32_t n_global, int apply) {
+// h->step is the (first) optimizer step this launch applies; n_steps > 1: steps h->step .. h->step + n_steps - 1.
+static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_local, uint32_t n_global, int apply,
+                            uint32_t n_steps = 1) {
     TrainArgs a{};
     a.in = q; a.targets = t; a.n_local = n_local; a.n_global = n_global;
     a.master = h->master; a.params = h->params; a.params_img = h->params_img; a.ema = h->ema; a.grads = h->grads;
@@ -376,8 +378,11 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
     a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
     // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double; h->step is the step being applied
-    a.ema_debias_old = 1.0f - (float)pow((double)h->ema_decay, (double)(h->step - 1));
-    a.ema_debias_new = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)h->step));
+    a.n_steps = n_steps;
+    for (uint32_t s = 0; s < n_steps && s < 4; ++s) {
+        a.ema_debias_old[s] = 1.0f - (float)pow((double)h->ema_decay, (double)(h->step + s - 1));
+        a.ema_debias_new[s] = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)(h->step + s)));
+    }
     a.apply = apply;
     a.timeline = h->timeline;
     a.perm_n = 0; a.perm_seed = 0; a.perm_base = 0;
@@ -532,6 +537,54 @@ int nrc_b200_propagate_train_radiance(const nrc_b200_suffix_end_vertex* end_vert
     return NRC_B200_OK;
 }
 uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed) { return permute16(i & 0xFFFFu, seed); }
+// Device::nrcTrainRadiance (Device.cpp:1482-1513): NUM_BATCHES consecutive train() calls, as ONE cooperative launch.
+int nrc_b200_train_batches(nrc_b200_handle h, const float* q, const float* t, int n_batches, void* cu_stream, float* loss_h) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    if (n_batches < 1 || n_batches > NRC_B200_NUM_BATCHES) return fail(NRC_B200_ERR_INVALID, "n_batches must be in [1, 4]");
+    if (h->dp_world > 1) return fail(NRC_B200_ERR_INVALID, "train_batches is single-GPU; use train_dp per batch");
+    if (h->encoding == NRC_B200_HASH) {
+        // Hash: the grid scatter makes a step 4x longer and the in-kernel barriers cost more than the launch gaps
+        // (measured 90 vs 76 us per step): keep one launch per batch, losses into loss4_d[b].
+        for (int b = 0; b < n_batches; ++b) {
+            h->step += 1;
+            h->barrier_total += NRC_B200_BATCH_SIZE / 128;
+            TrainArgs a = train_args(h, q + (size_t)b * NRC_B200_BATCH_SIZE * 15, t + (size_t)b * NRC_B200_BATCH_SIZE * 3,
+                                     NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1);
+            a.loss_out = h->loss4_d + b;
+            CU(launch_train_step(h->encoding, a, h->gm, h->stream));
+            h->launches += 1;
+        }
+        h->pending_tiles = 0;
+        if (loss_h) {
+            CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 4 * n_batches, cudaMemcpyDeviceToHost, h->stream));
+            CU(cudaStreamSynchronize(h->stream));
+            float l = 0.0f;
+            for (int b = 0; b < n_batches; ++b) l += h->loss_pinned[b];
+            *loss_h = l / (float)n_batches;
+        }
+        return NRC_B200_OK;
+    }
+    h->step += 1;
+    TrainArgs a = train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1, (uint32_t)n_batches);
+    a.barrier_target = h->barrier_total + NRC_B200_BATCH_SIZE / 128;
+    a.loss_out = h->loss4_d;
+    h->barrier_total += (2 * n_batches - 1) * (NRC_B200_BATCH_SIZE / 128);
+    h->step += n_batches - 1;
+    CU(launch_train_step(h->encoding, a, h->gm, h->stream));
+    h->launches += 1;
+    h->pending_tiles = 0;
+    if (loss_h) {  // mean of the per-batch losses, as Device::nrcTrainRadiance reports it
+        CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 4 * n_batches, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        float l = 0.0f;
+        for (int b = 0; b < n_batches; ++b) l += h->loss_pinned[b];
+        *loss_h = l / (float)n_batches;
+    }
+    return NRC_B200_OK;
+}
 int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
                                 int num_records, uint32_t seed, void* cu_stream) {
     if (!q_src_d || !t_src_d || !q_dst_d || !t_dst_d) return fail(NRC_B200_ERR_INVALID, "null device buffer");
@@ -607,9 +660,22 @@ int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream,
                                 f->num_tiles, h->stream));
             h->launches += 1;
         }
-        for (uint32_t b = 0; b < NRC_B200_NUM_BATCHES; ++b) {                       // nrcShuffleTrainingData + nrcTrainRadiance
-            int rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
-            if (rc != NRC_B200_OK) return rc;
+        if (h->dp_world > 1 || h->encoding == NRC_B200_HASH) {
+            for (uint32_t b = 0; b < NRC_B200_NUM_BATCHES; ++b) {                   // nrcShuffleTrainingData + nrcTrainRadiance
+                int rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
+                if (rc != NRC_B200_OK) return rc;
+            }
+        } else {                                                     // Frequency: the four steps in one launch
+            h->step += 1;
+            TrainArgs a = train_args(h, f->train_queries_d, f->train_targets_d, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, 1,
+                                     NRC_B200_NUM_BATCHES);
+            a.barrier_target = h->barrier_total + NRC_B200_BATCH_SIZE / 128;
+            a.perm_n = (uint32_t)n_rec; a.perm_seed = f->shuffle_seed; a.perm_base = 0;
+            a.loss_out = h->loss4_d;
+            h->barrier_total += (2 * NRC_B200_NUM_BATCHES - 1) * (NRC_B200_BATCH_SIZE / 128);
+            h->step += NRC_B200_NUM_BATCHES - 1;
+            CU(launch_train_step(h->encoding, a, h->gm, h->stream));
+            h->launches += 1;
         }
         if (stat) {
             CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 16, cudaMemcpyDeviceToHost, h->stream));

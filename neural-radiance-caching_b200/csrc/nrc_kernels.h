@@ -25,6 +25,7 @@ cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, 
 //   phase 2  grid barrier
 //   phase 3  every CTA reduces its slice of the gradient over all tiles (fixed order) and either applies
 //            Adam + EMA to that slice (apply = 1) or leaves the fp32 gradient for a data-parallel all-reduce (apply = 0).
+// The reference's per-frame loop of NUM_BATCHES train() calls (Device::nrcTrainRadiance) can run as one launch (n_steps).
 struct TrainArgs {
     const float* in; const float* targets;
     uint32_t n_local, n_global;      // samples of this launch / of the global batch (loss normalisation)
@@ -38,10 +39,15 @@ struct TrainArgs {
     float* grad_f32;                 // [n_params] reduced fp32 gradient (apply = 0: the all-reduce payload)
     float* loss_out;
     uint32_t* barrier_counter;       // monotonically increasing arrival counter
-    uint32_t barrier_target;         // value the counter reaches when every CTA of this launch has arrived
+    uint32_t barrier_target;         // value the counter reaches when every CTA has arrived at the launch's FIRST barrier
     uint32_t n_params, n_mlp;
-    float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale, ema_debias_old, ema_debias_new;
+    float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
+    float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
     int apply;
+    // n_steps optimizer steps in ONE launch (apply = 1, dp_world = 1): step s trains on samples [s*n_local, (s+1)*n_local)
+    // of `in` / `targets` (fused shuffle: destination indices perm_base + s*n_local + ...), writes its loss to
+    // loss_out[s]; two grid barriers per step (gradients complete / weights updated), the last one omitted.
+    uint32_t n_steps;
     long long* timeline;             // optional [n_tiles][8] clock64 stamps of the phases (debug), or nullptr
     // Data-parallel exchange fused into phase 3 (dp_world > 1, apply = 1): every rank pushes its slice gradients into
     // row `dp_rank` of EVERY peer's exchange buffer through NVLink peer pointers and sums the rows it received in rank

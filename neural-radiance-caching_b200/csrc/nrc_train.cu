@@ -95,7 +95,7 @@ __device__ __forceinline__ void mma_wgrad(uint32_t d, uint32_t delta_img, uint32
 // adam_step (tcnn/optimizers/adam.h:75-118) followed by ema_step_half_precision (ema.h:62-76).  `g32` is the
 // reduced fp32 gradient (loss-scaled); the reference's gradient buffer is fp16 (trainer.h:322-336), so it is
 // rounded to fp16 first.  Also maintains the UMMA image of the fp16 training weights.
-__device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E) {
+__device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E, uint32_t s = 0) {
     const __half gh = __float2half_rn(g32);
     a.grads[i] = gh;
     float gradient = __half2float(gh) / a.loss_scale;
@@ -116,14 +116,14 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
         a.params[i] = w_half;
         if (is_matrix) a.params_img[img_index(i, E)] = w_half;
     }
-    const float filtered = (__half2float(a.ema[i]) * a.ema_decay * a.ema_debias_old +
-                            __half2float(w_half) * (1.0f - a.ema_decay)) * a.ema_debias_new;
+    const float filtered = (__half2float(a.ema[i]) * a.ema_decay * a.ema_debias_old[s] +
+                            __half2float(w_half) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
     a.ema[i] = __float2half_rn(filtered);
 }
 
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
 // in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
-__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E) {
+__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s) {
     for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 8 * kTrainThreads) {
         float4 g[2], w[2], m1[2], m2[2];
         uint4 st[2];
@@ -169,8 +169,8 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                     wv[c] = wv[c] - eff * av[c];
                     pv[c] = __float2half_rn(wv[c]);
                 }
-                const float filtered = (__half2float(ev[c]) * a.ema_decay * a.ema_debias_old +
-                                        __half2float(pv[c]) * (1.0f - a.ema_decay)) * a.ema_debias_new;
+                const float filtered = (__half2float(ev[c]) * a.ema_decay * a.ema_debias_old[s] +
+                                        __half2float(pv[c]) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
                 ev[c] = __float2half_rn(filtered);
             }
             *reinterpret_cast<float4*>(a.grad_f32 + i) = g[u];
@@ -193,8 +193,8 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
 #define NRCB_SCATTER_AGG 1
 #endif
 // ---------------------------------------------------------------- the step kernel
-template <int ENC>
-__global__ void __launch_bounds__(kTrainThreads, 1)
+template <int ENC, bool MULTI>   // MULTI: a.n_steps optimizer steps in this launch (separate instantiation: the loop costs the
+__global__ void __launch_bounds__(kTrainThreads, 1)   // single-step Hash kernel registers in its scatter loop)
 nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     constexpr int E = ENC == 0 ? 80 : 64;
     constexpr int NMLP = 64 * E + 4 * 4096 + 1024;
@@ -213,18 +213,13 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const uint32_t tile = blockIdx.x;
     const uint32_t n_tiles = gridDim.x;
     const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0 && a.perm_n == 0;   // bulk copy needs a contiguous tile
-    auto stamp = [&](int slot) { if (a.timeline && tid == 0) a.timeline[tile * 8 + slot] = clock64(); };
+    uint32_t s = 0;                 // optimizer step within this launch
+    auto stamp = [&](int slot) { if (a.timeline && tid == 0 && s == 0) a.timeline[tile * 8 + slot] = clock64(); };
     stamp(0);
 
     if (tid == 0) {
         mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1);
         fence_mbar_init();
-        mbar_arrive_expect_tx(w_full, L::kWbytes);
-        bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
-        if (in_aligned) {
-            mbar_arrive_expect_tx(in_full, 7680);
-            bulk_g2s(smem + L::kIn, a.in + (size_t)tile * kTT * 15, 7680, in_full);
-        }
     }
     if (warp == kWorkerWarps) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
@@ -233,6 +228,21 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t sW = smem_u32(smem + L::kW), sX = smem_u32(smem + L::kX), sH = smem_u32(smem + L::kH);
     const uint32_t sDl = smem_u32(smem + L::kDelta), sG = smem_u32(smem + L::kG);
+    const uint32_t n_steps = MULTI ? a.n_steps : 1;
+
+  for (s = 0; s < n_steps; ++s) {
+    const uint32_t first = s * a.n_local + tile * kTT;   // first sample of this tile in this step
+    if (tid == 0) {
+        // s > 0: the weight image was rewritten with generic stores by every CTA in the previous step; the grid barrier
+        // ordered them, this makes them visible to the bulk copy (async proxy).
+        if (s > 0) asm volatile("fence.proxy.async;" ::: "memory");
+        mbar_arrive_expect_tx(w_full, L::kWbytes);
+        bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
+        if (in_aligned) {
+            mbar_arrive_expect_tx(in_full, 7680);
+            bulk_g2s(smem + L::kIn, a.in + (size_t)first * 15, 7680, in_full);
+        }
+    }
 
     if (warp == kWorkerWarps) {
         // ======================= MMA issuer =======================
@@ -240,7 +250,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         uint32_t ph = 0;
         auto wait_workers = [&]() { mbar_wait_uniform(a_ready, ph); ph ^= 1; tc_fence_after(); };
         const uint32_t acc = tmem_base + kAcc;
-        mbar_wait(w_full, 0);              // weight image landed (async proxy write -> async proxy read)
+        mbar_wait(w_full, s & 1);          // weight image landed (async proxy write -> async proxy read)
         // forward
         wait_workers();
         if (leader) { mma_fwd(acc, sX, sW, 64, E / 16); umma_commit(d_ready); }
@@ -292,10 +302,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         auto signal = [&]() { fence_proxy_async_smem(); tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(a_ready); };
 
         // source record of this sample: contiguous, or gathered through the per-frame permutation (fused shuffle)
-        const uint32_t src_row = a.perm_n ? permute16(a.perm_base + tile * kTT + row, a.perm_seed) % a.perm_n : tile * kTT + row;
+        const uint32_t src_row = a.perm_n ? permute16(a.perm_base + first + row, a.perm_seed) % a.perm_n : first + row;
         float q[15];
         if (in_aligned) {
-            mbar_wait(in_full, 0);
+            mbar_wait(in_full, s & 1);
             const float* s_in = reinterpret_cast<const float*>(smem + L::kIn);
 #pragma unroll
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
@@ -480,11 +490,11 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                 }
 #ifdef NRCB_DEBUG_LEVELS
-                if (a.timeline && tid == 0) a.timeline[tile * 8 + j] = clock64();
+                if (a.timeline && tid == 0 && s == 0) a.timeline[tile * 8 + j] = clock64();
 #endif
             }
         }
-        if (a.timeline && tid == 128) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
+        if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
         // per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.
         // The TMEM loads are warp-wide (.sync.aligned): every lane executes them, lanes 0..15 store.
         // Column chunks of 16 are split between the two halves.
@@ -522,21 +532,21 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             }
         }
     }
-    // ---- phase 2: publish this tile's partials, free TMEM, wait for every tile of the batch
+    // ---- phase 2: publish this tile's partials, wait for every tile of the batch
     stamp(4);
     __threadfence();
     tc_fence_before();
     __syncthreads();
-    if (warp == kWorkerWarps) tmem_dealloc(tmem_base, 512);
     if (tid == 0) {
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
         uint32_t seen, spins = 0;
         do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
             if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-        } while ((int32_t)(seen - a.barrier_target) < 0);
+        } while ((int32_t)(seen - (a.barrier_target + 2 * s * n_tiles)) < 0);
     }
     __syncthreads();
+    tc_fence_after();
     stamp(5);
 
     // ---- phase 3: slice c of the gradient: fixed-order sum over tiles, then Adam + EMA (or store for all-reduce)
@@ -580,10 +590,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             for (uint32_t j = tid; j < hi - lo; j += kTrainThreads) {
                 const float g = slice_grad(j);
                 a.grad_f32[lo + j] = g;
-                if (a.apply) adam_ema_param(a, lo + j, g, E);
+                if (a.apply) adam_ema_param(a, lo + j, g, E, s);
             }
             if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
-                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E);
+                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s);
                 else
                     for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) a.grad_f32[NMLP + j] = __ldcg(a.grid_grad + j);
             }
@@ -592,7 +602,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 for (uint32_t t = lane; t < n_tiles; t += 32) l += __ldcg(a.loss_partials + t);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-                if (lane == 0) *a.loss_out = l;
+                if (lane == 0) a.loss_out[s] = l;
             }
         } else {
             // ---- data parallel: the all-reduce happens here, over NVLink peer memory.
@@ -675,6 +685,26 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     }
     __syncthreads();
     stamp(6);
+    if (s + 1 < n_steps) {
+        // ---- every CTA has applied its slice: the next step may read the new weights (and reuse the partials buffer)
+        __threadfence();
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
+            uint32_t seen, spins = 0;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
+                if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+            } while ((int32_t)(seen - (a.barrier_target + (2 * s + 1) * n_tiles)) < 0);
+            __threadfence();
+        }
+        __syncthreads();
+    }
+  }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kWorkerWarps) tmem_dealloc(tmem_base, 512);
 }
 
 // ---------------------------------------------------------------- stand-alone optimizer (data-parallel path)
@@ -699,14 +729,17 @@ static cudaError_t launch_train_t(const TrainArgs& a, const GridMeta& gm, cudaSt
     using L = TrainSmem<ENC == 0 ? 80 : 64>;
     static bool configured[2] = {false, false};
     if (!configured[ENC]) {
-        cudaError_t e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+        cudaError_t e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
         if (e != cudaSuccess) return e;
         configured[ENC] = true;
     }
     // Cooperative launch: the grid barrier needs every CTA resident (<= 128 CTAs, one per SM).
     void* args[2] = {const_cast<TrainArgs*>(&a), const_cast<GridMeta*>(&gm)};
-    return cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC>), dim3(a.n_local / kTT),
-                                       dim3(kTrainThreads), args, L::kTotal, stream);
+    const bool multi = a.apply && a.dp_world <= 1 && a.n_steps > 1;
+    const void* fn = multi ? reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, true>)
+                           : reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, false>);
+    return cudaLaunchCooperativeKernel(fn, dim3(a.n_local / kTT), dim3(kTrainThreads), args, L::kTotal, stream);
 }
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
     return encoding == 0 ? launch_train_t<0>(a, gm, stream) : launch_train_t<1>(a, gm, stream);

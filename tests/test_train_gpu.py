@@ -140,3 +140,48 @@ def test_set_learning_rate(pkg):
     net.setHyperParams(pkg.HyperParams(5e-4))
     assert abs(net.getLearningRate() - 5e-4) < 1e-9
     net.destroy()
+
+
+@pytest.mark.parametrize("enc", [0, 1])
+def test_train_batches_is_the_loop_of_train_calls(pkg, synth, enc):
+    """nrc_b200_train_batches (Frequency: four optimizer steps in one cooperative launch, grid barriers between them; Hash:
+    one launch per batch) must leave exactly the state that four nrc_b200_train calls leave: weights, EMA weights,
+    gradients, losses -- bit for bit for Frequency; the Hash grid gradient is summed with fp32 atomics whose order varies
+    from run to run, so Hash is compared at the tolerance two identical runs show."""
+    import torch
+    q = np.concatenate([synth.cornell_queries(B, seed=70 + b) for b in range(4)])
+    t = synth.radiance_targets(q, seed=70)
+    qd, td = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+    nets = []
+    for mode in ("loop", "fused"):
+        net = pkg.Network()
+        net.init(0, enc, seed=11)
+        if enc == 1:
+            master = net.get_params(pkg.PARAMS_MASTER_F32)
+            nm = net.n_params()[1]
+            master[nm:] = np.random.default_rng(3).uniform(-0.1, 0.1, master.size - nm).astype(np.float32)
+            net.load_master(master)
+        for rep in range(2):   # two frames: the second starts from non-trivial optimizer state
+            if mode == "loop":
+                losses = [net.train(qd[b * B:(b + 1) * B], td[b * B:(b + 1) * B], want_loss=True) for b in range(4)]
+                loss = float(np.mean(np.array(losses, dtype=np.float32)))
+            else:
+                loss = net.train_batches(qd, td, 4, want_loss=True)
+        nets.append((net, loss))
+    (a, la), (b, lb) = nets
+    if enc == 1:
+        assert abs(la - lb) <= 2e-3 * abs(la), (la, lb)
+        nm = a.n_params()[1]
+        wa, wb = a.get_params(pkg.PARAMS_MASTER_F32), b.get_params(pkg.PARAMS_MASTER_F32)
+        assert np.abs(wa[:nm] - wb[:nm]).max() <= 2e-2 * np.abs(wa[:nm]).max()
+        assert np.quantile(np.abs(wa[nm:] - wb[nm:]), 0.999) <= 1e-3
+        return
+    assert abs(la - lb) <= 1e-6 * abs(la), (la, lb)
+    for kind in (pkg.PARAMS_MASTER_F32, pkg.PARAMS_EMA_F16, pkg.PARAMS_TRAIN_F16, pkg.PARAMS_GRAD_F16):
+        pa, pb = a.get_params(kind), b.get_params(kind)
+        assert np.array_equal(pa.view(np.uint8), pb.view(np.uint8)), f"kind {kind}: {np.mean(pa != pb)} of the entries differ"
+    # and the EMA weights drive the same queries to the same radiance
+    probe = torch.from_numpy(synth.cornell_queries(4096, seed=5)).cuda()
+    oa, ob = torch.empty(4096, 3, device="cuda"), torch.empty(4096, 3, device="cuda")
+    a.infer(probe, oa, 4096); b.infer(probe, ob, 4096)
+    assert torch.equal(oa, ob)
