@@ -3,25 +3,32 @@
 // trim_and_cast  (tcnn/src/fully_fused_mlp.cu:499-557, nrc/src/NRCNetwork.cu:64-83)
 // with ONE persistent kernel: encoded features and activations never touch HBM.
 //
-// CTA = 4 MMA-issue warps + 4 groups x 4 worker warps. Each group owns one 128-query tile at a time:
-//   workers : bulk-copy the tile's 7680 input bytes to smem, encode in registers, write the fp16 features
-//             into TMEM as the A operand, then per layer read the fp32 accumulator from TMEM, ReLU, round to
-//             fp16 and write it back to TMEM as the next layer's A operand.
-//   MMA warp g: one elected thread issues tcgen05.mma.kind::f16 (M=128 queries, N=64|16, K=16) with A from TMEM
-//             and the layer's weight matrix (resident in smem for the whole kernel) as B; completion is
-//             signalled to the group through tcgen05.commit -> mbarrier.
-// Four tiles are in flight per SM so the tensor pipe, the TMEM ports and the FP32 pipes overlap.
+// CTA = 5 groups x 4 warps (640 threads). Each group owns one 128-query tile at a time; five tiles are in flight per SM
+// (TMEM: 64 fp32 accumulator + 32 operand columns per tile) so that the tensor pipe, the TMEM ports and the FP32 pipes
+// overlap across groups:
+//   all warps : bulk-copy the tile's 7680 input bytes to smem, encode in registers, write the fp16 features as the
+//               K-major A image of the input layer to shared memory (80 features would need 40 TMEM columns and cap
+//               the SM at four tiles); then per layer read the fp32 accumulator from TMEM, ReLU, round to fp16 and
+//               write it back to TMEM as the next layer's A operand (the activations never leave the SM).
+//   warp 0 of the group additionally issues the layer: after a named barrier tells it that the A operand is complete,
+//               one elected lane issues tcgen05.mma.kind::f16 (M=128 queries, N=64|16, K=16; A from shared memory for
+//               the input layer, from TMEM for the others; B = the layer's weight matrix, resident in smem for the
+//               whole kernel), commits to an mbarrier, waits for it and releases the other three warps through a
+//               second named barrier (only one warp per group polls; the others block in bar.sync, which costs no
+//               issue slots -- with dedicated issuer warps and every worker polling, 28 % of all issued instructions
+//               were polls; profiles/r01_infer_experiments.md).
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
+#include <type_traits>
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
 
 namespace nrcb {
 
-constexpr int kGroups = 4;
+constexpr int kGroups = 5;
 constexpr int kTile = 128;
-constexpr int kThreads = kGroups * 32 + kGroups * 128;  // 4 issuer warps + 16 worker warps
-constexpr uint32_t kTmemGroupCols = 128;  // per group: D at +0 (64 cols), A at +64 (40 cols)
+constexpr int kThreads = kGroups * 128;
+constexpr uint32_t kTmemGroupCols = 96;   // per group: D at +0 (64 columns), A at +64 (32 columns)
 constexpr uint32_t kTmemA = 64;
 
 template <int E>
@@ -32,12 +39,17 @@ struct InferSmem {
     static constexpr int kWeights = kWin + kWhid + kWout;
     static constexpr int kStage = kTile * 15 * 4;     // 7680 B of raw queries per group
     static constexpr int kOut = kTile * 3 * 4;        // 1536 B of results per group
-    static constexpr int kInOff = kWeights;
+    // Frequency only (E = 80): encoded tile = K-major A image of the input layer, per group.  Hash features (E = 64) fit
+    // the 32 operand columns in TMEM, and its gathers want the shared-memory carve-out small (L1 capacity).
+    static constexpr int kA0 = E > 64 ? kTile * E * 2 : 0;
+    static constexpr int kA0Off = kWeights;
+    static constexpr int kInOff = kA0Off + kGroups * kA0;
     static constexpr int kOutOff = kInOff + kGroups * kStage;
     static constexpr int kAcc = kTile * 12 + kTile * 16;   // fused accumulation: throughput (1536 B) + output (2048 B) of a tile
-    static constexpr int kAccOff = kOutOff + kGroups * kOut;           // [kGroups][2 parities][kAcc]
-    static constexpr int kBarOff = kAccOff + kGroups * 2 * kAcc;
-    static constexpr int kTotal = kBarOff + 256;
+    static constexpr int kBarOff = kOutOff + kGroups * kOut;
+    static constexpr int kAccOff = kBarOff + 256;                      // [kGroups][2 parities][kAcc], only with accumulation
+    static constexpr int kTotalNoAcc = kAccOff;                        // launches without accumulation leave more L1
+    static constexpr int kTotal = kAccOff + kGroups * 2 * kAcc;
 };
 
 // Copies one row-major fp16 matrix W[n_out][n_in] into the UMMA K-major interleaved image:
@@ -52,52 +64,37 @@ __device__ __forceinline__ void stage_weight(uint8_t* dst, const __half* __restr
     }
 }
 
-__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
+// Named barriers of group g (128 threads each): 1 + g "A operand ready", 1 + kGroups + g "accumulator ready" / group sync.
+__device__ __forceinline__ void bar_sync_id(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void bar_arrive_id(int id) { asm volatile("bar.arrive %0, 128;" ::"r"(id) : "memory"); }
 
-// MMA issuer of group G. Everything the MMAs consume is warp-uniform and derived from compile-time group /
-// layer indices, so ptxas keeps the operands in uniform registers and emits back-to-back UTCHMMA (a
-// data-dependent scheduler here cost ~150 cycles per MMA in R2UR + elect waterfalls; measured, profiles/).
-template <int ENC, int G>
-__device__ __forceinline__ void mma_issuer(uint8_t* smem, uint32_t tmem_base, uint64_t* a_ready, uint64_t* d_ready,
-                                           uint32_t n_tiles, uint32_t tile_stride) {
+// One layer of the group's tile, issued by a single elected lane.  LY is a compile-time constant so every descriptor is
+// a uniform-register immediate offset and ptxas emits back-to-back UTCHMMA.
+template <int ENC, int LY>
+__device__ __forceinline__ void issue_layer(uint32_t sbase, uint32_t a0, uint32_t dD, uint64_t* d_ready) {
     constexpr int E = ENC == 0 ? 80 : 64;
-    constexpr int KS0 = E / 16;
     using L = InferSmem<E>;
     constexpr uint32_t idesc64 = umma_idesc_f16(128, 64, 0, 0);
     constexpr uint32_t idesc16 = umma_idesc_f16(128, 16, 0, 0);
-    const uint32_t sbase = smem_u32(smem);
-    const uint64_t d_in = umma_desc(sbase, 64 * 16, 128);
-    const uint64_t d_hid = umma_desc(sbase + L::kWin, 64 * 16, 128);
-    const uint64_t d_out = umma_desc(sbase + L::kWin + L::kWhid, 16 * 16, 128);
-    const uint32_t dD = tmem_base + G * kTmemGroupCols;
     const uint32_t dA = dD + kTmemA;
-    const uint32_t first = blockIdx.x * kGroups + G;
-    const uint32_t nt = first < n_tiles ? (n_tiles - first + tile_stride - 1) / tile_stride : 0;
-    const bool leader = elect_one();
-    uint32_t ph = 0;
-    for (uint32_t it = 0; it < nt; ++it) {
+    if constexpr (LY == 0) {
+        const uint64_t d_a0 = umma_desc(a0, 2048, 128);   // K-major A [128 x E]: +4096 B per k-step
+        const uint64_t d_in = umma_desc(sbase, 64 * 16, 128);
 #pragma unroll
-        for (int ly = 0; ly < 6; ++ly) {
-            mbar_wait_uniform(&a_ready[G], ph);
-            ph ^= 1;
-            tc_fence_after();
-            if (leader) {
-                if (ly == 0) {
-#pragma unroll
-                    for (int k = 0; k < KS0; ++k) umma_ts(dD, dA + 8 * k, d_in + (uint64_t)(k * 128), idesc64, k > 0);
-                } else if (ly < 5) {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        umma_ts(dD, dA + 8 * k, d_hid + (uint64_t)((ly - 1) * 512 + k * 128), idesc64, k > 0);
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) umma_ts(dD, dA + 8 * k, d_out + (uint64_t)(k * 32), idesc16, k > 0);
-                }
-                umma_commit(&d_ready[G]);
-            }
-            __syncwarp();
+        for (int k = 0; k < E / 16; ++k) {
+            if constexpr (L::kA0 != 0) umma_ss(dD, d_a0 + (uint64_t)(k * 256), d_in + (uint64_t)(k * 128), idesc64, k > 0);
+            else umma_ts(dD, dA + 8 * k, d_in + (uint64_t)(k * 128), idesc64, k > 0);
         }
+    } else if constexpr (LY < 5) {
+        const uint64_t d_hid = umma_desc(sbase + L::kWin + (LY - 1) * 8192, 64 * 16, 128);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ts(dD, dA + 8 * k, d_hid + (uint64_t)(k * 128), idesc64, k > 0);
+    } else {
+        const uint64_t d_out = umma_desc(sbase + L::kWin + L::kWhid, 16 * 16, 128);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ts(dD, dA + 8 * k, d_out + (uint64_t)(k * 32), idesc16, k > 0);
     }
+    umma_commit(d_ready);
 }
 
 template <int ENC>  // 0 = Frequency (E = 80), 1 = Hash (E = 64)
@@ -109,9 +106,8 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     extern __shared__ __align__(1024) uint8_t smem[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
     uint64_t* in_full = bars;              // [kGroups] raw tile landed in smem
-    uint64_t* a_ready = bars + kGroups;    // [kGroups] A operand (and D drained) ready for the next layer's MMA
-    uint64_t* d_ready = bars + 2 * kGroups;  // [kGroups] accumulator complete
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGroups);
+    uint64_t* d_ready = bars + kGroups;    // [kGroups] accumulator complete
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kGroups);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
@@ -126,7 +122,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         stage_weight(smem + L::kWin + L::kWhid, W, 16, 64, tid, kThreads);
     }
     if (tid == 0) {
-        for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&a_ready[g], 4); mbar_init(&d_ready[g], 1); }
+        for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&d_ready[g], 1); }
         fence_mbar_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, 512);
@@ -136,31 +132,29 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp < kGroups) {
-        // ======================= MMA issuers: warp g serves group g =======================
-        if (warp == 0) mma_issuer<ENC, 0>(smem, tmem_base, a_ready, d_ready, n_tiles, tile_stride);
-        else if (warp == 1) mma_issuer<ENC, 1>(smem, tmem_base, a_ready, d_ready, n_tiles, tile_stride);
-        else if (warp == 2) mma_issuer<ENC, 2>(smem, tmem_base, a_ready, d_ready, n_tiles, tile_stride);
-        else mma_issuer<ENC, 3>(smem, tmem_base, a_ready, d_ready, n_tiles, tile_stride);
-    } else {
-        // ======================= workers =======================
-        const int g = (warp - kGroups) >> 2;
-        const int gtid = tid - kGroups * 32 - g * 128;            // 0..127 within the group
+    {
+        const int g = warp >> 2;
+        const int gtid = tid & 127;                     // 0..127 within the group
         const uint32_t row = (warp & 3) * 32 + lane;    // TMEM lane == query row inside the tile
-        const uint32_t tD = tmem_base + g * kTmemGroupCols + (((warp & 3) * 32u) << 16);
+        const uint32_t dD = tmem_base + g * kTmemGroupCols;             // accumulator, lane 0 (MMA addresses)
+        const uint32_t tD = dD + (((warp & 3) * 32u) << 16);            // this warp's lane quadrant
         const uint32_t tA = tD + kTmemA;
+        const uint32_t a0 = smem_u32(smem + L::kA0Off + g * L::kA0);
+        uint8_t* a_row = smem + L::kA0Off + g * L::kA0 + (row >> 3) * 128 + (row & 7) * 16;   // chunk c of this row at + c*2048
         float* s_in = reinterpret_cast<float*>(smem + L::kInOff + g * L::kStage);
         float* s_out = reinterpret_cast<float*>(smem + L::kOutOff + g * L::kOut);
+        uint8_t* s_acc = smem + L::kAccOff + g * 2 * L::kAcc;
+        const uint32_t sbase = smem_u32(smem);
+        const __half2* grid = reinterpret_cast<const __half2*>(params + (64 * E + 4 * 4096 + 16 * 64));
         const bool in_bulk_ok = (reinterpret_cast<uintptr_t>(in) & 15) == 0;
         const bool out_vec_ok = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
-
-        uint8_t* s_acc = smem + L::kAccOff + g * 2 * L::kAcc;
         const bool acc_bulk_ok = acc.out != nullptr && (reinterpret_cast<uintptr_t>(acc.throughput) & 15) == 0 &&
                                  (reinterpret_cast<uintptr_t>(acc.out) & 15) == 0;
         // tiles whose 128 queries are all pixels prefetch throughput + output rows with the same mbarrier as the input
         auto acc_staged = [&](uint32_t t) { return acc_bulk_ok && in_bulk_ok && (t + 1) * kTile <= acc.n && (t + 1) * kTile <= n; };
+        const int bar_a = 1 + g, bar_d = 1 + kGroups + g;
 
-        auto load_tile = [&](uint32_t t, uint32_t par) {  // called by all 128 threads of the group, after a group_sync
+        auto load_tile = [&](uint32_t t, uint32_t par) {  // called by all 128 threads of the group, after a group sync
             const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
             const float* src = in + (size_t)t * kTile * 15;
             if (in_bulk_ok && rows == kTile) {
@@ -175,13 +169,46 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 }
             } else {  // ragged tail / unaligned caller buffer: plain loads, zero-fill the missing rows
                 for (uint32_t i = gtid; i < kTile * 15; i += 128) s_in[i] = i < rows * 15 ? __ldg(src + i) : 0.0f;
-                group_sync(g);
+                bar_sync_id(bar_d);
                 if (gtid == 0) mbar_arrive(&in_full[g]);
             }
         };
 
+        uint32_t ph_d = 0;
+        // The A operand of layer LY is complete (shared memory for the input layer, TMEM otherwise) and the accumulator is
+        // drained: run the layer, return when its accumulator is complete.
+        auto run_layer = [&](auto LY) {
+            if (decltype(LY)::value == 0 && L::kA0 != 0) fence_proxy_async_smem();   // feature image: generic writes -> tensor pipe
+            else tmem_wait_st();
+            tc_fence_before();
+            if ((warp & 3) == 0) {
+                bar_sync_id(bar_a);
+                tc_fence_after();
+                if (elect_one()) issue_layer<ENC, decltype(LY)::value>(sbase, a0, dD, &d_ready[g]);
+                __syncwarp();
+                mbar_wait(&d_ready[g], ph_d);
+                bar_sync_id(bar_d);
+            } else {
+                bar_arrive_id(bar_a);
+                bar_sync_id(bar_d);
+            }
+            ph_d ^= 1;
+            tc_fence_after();
+        };
+        auto hidden_epilogue = [&]() {   // D (fp32) -> relu -> fp16 -> A
+#pragma unroll
+            for (int hcol = 0; hcol < 2; ++hcol) {
+                uint32_t v[32], w[16];
+                tmem_ld32(tD + hcol * 32, v);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+                tmem_st16(tA + hcol * 16, w);
+            }
+        };
+
         uint32_t t = blockIdx.x * kGroups + g;
-        uint32_t ph_in = 0, ph_d = 0, par = 0;
+        uint32_t ph_in = 0, par = 0;
         if (t < n_tiles) load_tile(t, 0);
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
@@ -189,58 +216,44 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
 #pragma unroll
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
             fence_proxy_async_smem();                        // order these generic reads before the next bulk write
-            group_sync(g);                                   // everyone holds its query: the stage is free
+            bar_sync_id(bar_d);                              // everyone holds its query: the stage is free
             if (t + tile_stride < n_tiles) load_tile(t + tile_stride, par ^ 1);
 
-            // ---- encode -> A operand of the input layer
+            // ---- encode -> A operand of the input layer (its previous contents were consumed long ago)
             {
                 uint32_t e[E / 2];
                 if constexpr (ENC == 0) encode_frequency(q, e);
-                else encode_hash(q, reinterpret_cast<const __half2*>(params + (64 * E + 4 * 4096 + 16 * 64)), gm, e);
+                else encode_hash(q, grid, gm, e);
+                if constexpr (L::kA0 != 0) {
 #pragma unroll
-                for (int c = 0; c < E / 16; ++c) {
-                    uint32_t v[8];
+                    for (int c = 0; c < E / 8; ++c)
+                        *reinterpret_cast<uint4*>(a_row + c * 2048) = make_uint4(e[4 * c], e[4 * c + 1], e[4 * c + 2], e[4 * c + 3]);
+                } else {
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) v[i] = e[c * 8 + i];
-                    tmem_st8(tA + c * 8, v);
+                    for (int c = 0; c < E / 16; ++c) {
+                        uint32_t v[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) v[i] = e[c * 8 + i];
+                        tmem_st8(tA + c * 8, v);
+                    }
                 }
             }
-            tmem_wait_st();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&a_ready[g]);
-
-            // ---- 5 hidden layers: D (fp32) -> relu -> fp16 -> A
-#pragma unroll 1
-            for (int l = 0; l < 5; ++l) {
-                mbar_wait(&d_ready[g], ph_d); ph_d ^= 1;
-                tc_fence_after();
-#pragma unroll
-                for (int hcol = 0; hcol < 2; ++hcol) {
-                    uint32_t v[32], w[16];
-                    tmem_ld32(tD + hcol * 32, v);
-                    tmem_wait_ld();
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-                    tmem_st16(tA + hcol * 16, w);
-                }
-                tmem_wait_st();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&a_ready[g]);
-            }
+            run_layer(std::integral_constant<int, 0>{}); hidden_epilogue();
+            run_layer(std::integral_constant<int, 1>{}); hidden_epilogue();
+            run_layer(std::integral_constant<int, 2>{}); hidden_epilogue();
+            run_layer(std::integral_constant<int, 3>{}); hidden_epilogue();
+            run_layer(std::integral_constant<int, 4>{}); hidden_epilogue();
             // ---- output layer: relu, fp16 rounding (the reference's output is half), first 3 of 16 lanes
-            mbar_wait(&d_ready[g], ph_d); ph_d ^= 1;
-            tc_fence_after();
+            run_layer(std::integral_constant<int, 5>{});
             float y[3];
             {
-                uint32_t v[16];
-                tmem_ld16(tD, v);
+                uint32_t v[4];
+                tmem_ld4(tD, v);
                 tmem_wait_ld();
 #pragma unroll
                 for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
             }
-            // D is drained; the next tile's first arrive (after its encode) re-arms the MMA warp.
+            // D is drained: the next tile's first run_layer orders this read before the MMA that overwrites it.
             const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
             // Fused accumulate_render_radiance (nrc_helpers.cu:77-129) for the pixel queries: the radiance is still in
             // registers, so the separate pass (re-read 12 B radiance, 12 B throughput, 16 B output per pixel) disappears.
@@ -272,7 +285,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             float* dst = out + (size_t)t * kTile * 3;
             if (out_vec_ok && rows == kTile) {
                 s_out[row * 3 + 0] = y[0]; s_out[row * 3 + 1] = y[1]; s_out[row * 3 + 2] = y[2];
-                group_sync(g);
+                bar_sync_id(bar_d);
                 if (gtid < 96) reinterpret_cast<float4*>(dst)[gtid] = reinterpret_cast<const float4*>(s_out)[gtid];
             } else if (row < rows) {
                 dst[row * 3 + 0] = y[0]; dst[row * 3 + 1] = y[1]; dst[row * 3 + 2] = y[2];
@@ -296,7 +309,7 @@ static cudaError_t launch_infer_t(const float* in, float* out, uint32_t n, const
     }
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
     const uint32_t grid = min((uint32_t)num_sms, (n_tiles + kGroups - 1) / kGroups);
-    nrc_infer_kernel<ENC><<<grid, kThreads, L::kTotal, stream>>>(in, out, n, params, gm, acc);
+    nrc_infer_kernel<ENC><<<grid, kThreads, acc.out ? L::kTotal : L::kTotalNoAcc, stream>>>(in, out, n, params, gm, acc);
     return cudaGetLastError();
 }
 

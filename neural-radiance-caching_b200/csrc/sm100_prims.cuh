@@ -130,6 +130,26 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8])
                  "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
                  : "memory");
 }
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,"
+        "%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+        "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[4]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld2(uint32_t taddr, uint32_t (&r)[2]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr) : "memory");
+}
 
 // --------------------------------------------------------- UMMA descriptors
 // Shared-memory matrix descriptor, SWIZZLE_NONE ("interleaved") canonical layout, sm_100 version 1.
@@ -154,6 +174,12 @@ __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, int a_mn_maj
            | ((uint32_t)b_mn_major << 16)
            | ((uint32_t)(N >> 3) << 17)
            | ((uint32_t)(M >> 4) << 24);
+}
+// Same with an fp16 accumulator: D is stored as packed half2, two N elements per 32-bit TMEM column (the layout of a
+// TMEM A operand), rounded to fp16 after every K=16 instruction -- the arithmetic of the reference's
+// wmma::accumulator<__half> fragments (tcnn fully_fused_mlp.cu:68).
+__host__ __device__ constexpr uint32_t umma_idesc_f16_acc16(int M, int N, int a_mn_major, int b_mn_major) {
+    return umma_idesc_f16(M, N, a_mn_major, b_mn_major) & ~(3u << 4);
 }
 // D[tmem] (+)= A[smem] * B[smem]^T     (one elected thread)
 __device__ __forceinline__ void umma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,

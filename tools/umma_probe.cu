@@ -138,8 +138,10 @@ static double cmp_map(const std::vector<float>& dump, int ncols, const std::vect
 
 static int run_func(const std::string& name) {
     int M = 128, N = 64, K = 64;
-    bool a_tmem = false, mn = false;
+    bool a_tmem = false, mn = false, f16acc = false;
     if (name == "ss_k") {}
+    else if (name == "ts_f16acc") { a_tmem = true; f16acc = true; }
+    else if (name == "ts_f16acc_n16") { a_tmem = true; f16acc = true; N = 16; }
     else if (name == "ss_k80") { K = 80; }
     else if (name == "ss_n16") { N = 16; }
     else if (name == "ts") { a_tmem = true; }
@@ -189,6 +191,7 @@ static int run_func(const std::string& name) {
         p.b_sbo = K / 8 * 128; p.b_lbo = 128; p.b_kstep = 256;
         p.idesc = umma_idesc_f16(M, N, 1, 1);
     }
+    if (f16acc) p.idesc &= ~(3u << 4);   // D format f16
     p.a_bytes = a_tmem ? 0 : (uint32_t)aimg.size();
     p.b_bytes = (uint32_t)bimg.size();
     uint8_t *da, *db; float* dd;
@@ -202,6 +205,29 @@ static int run_func(const std::string& name) {
     CK(cudaDeviceSynchronize());
     std::vector<float> dump((size_t)128 * p.n_cols);
     CK(cudaMemcpy(dump.data(), dd, dump.size() * 4, cudaMemcpyDeviceToHost));
+    if (f16acc) {   // which 16-bit slot of which column holds D[row][n]?  try the plausible layouts
+        auto half_at = [&](int lane, int col, int hi) {
+            uint32_t w; memcpy(&w, &dump[(size_t)lane * p.n_cols + col], 4);
+            return h2f((uint16_t)(hi ? (w >> 16) : (w & 0xFFFF)));
+        };
+        double eP = 0, eU = 0, eS = 0;
+        for (int r = 0; r < M; ++r)
+            for (int n = 0; n < N; ++n) {
+                const double ex = E[(size_t)r * N + n], tol = 0;
+                (void)tol;
+                eP = fmax(eP, fabs(half_at(r, n / 2, n & 1) - ex));            // packed pairs (2c, 2c+1)
+                eU = fmax(eU, fabs(half_at(r, n, 0) - ex));                    // one element per column, low half
+                eS = fmax(eS, fabs(half_at(r, n % (N / 2), n / (N / 2)) - ex)); // split halves (c, c + N/2)
+            }
+        printf("case %-12s M=%d N=%d K=%d idesc=%08x  err packed(2c,2c+1)=%.4g  err unpacked(low half)=%.4g  err split(c,c+N/2)=%.4g\n",
+               name.c_str(), M, N, K, p.idesc, eP, eU, eS);
+        printf("  row 0 raw:");
+        for (int c = 0; c < 6; ++c) printf(" [%g %g]", half_at(0, c, 0), half_at(0, c, 1));
+        printf("\n  expected :");
+        for (int n = 0; n < 12; ++n) printf(" %g", E[n]);
+        printf("\n");
+        return 0;
+    }
     double e0 = cmp_map(dump, p.n_cols, E, M, N, 0), e1 = cmp_map(dump, p.n_cols, E, M, N, 1);
     int untouched = 0;
     for (int l = 0; l < 128; ++l) if (dump[(size_t)l * p.n_cols] == 12345.0f) untouched++;
