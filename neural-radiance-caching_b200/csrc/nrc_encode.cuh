@@ -83,10 +83,14 @@ __device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t 
 }
 
 // One level of the hash grid: trilinear interpolation of half2 features, accumulated with half2 fma
-// exactly like the reference (grid.h:146-163: result = fma((T)weight, grid_val, result)).
+// exactly like the reference (grid.h:146-163: result = fma((T)weight, grid_val, result); corner c = dx + 2 dy + 4 dz,
+// weight = ((1 * fx) * fy) * fz).
 // NC = true: read-only (ld.global.nc) loads -- query kernel; false: coherent loads -- the training kernel updates the
 // table later in the same launch.
-template <bool NC = true>
+// The per-axis index terms are computed once per level (2 values per axis, already masked: & distributes over ^), so a
+// corner costs one 3-input LOP3 (hashed) or one IADD3 + mask (dense) instead of two multiplies and two xors.
+// LVL is the compile-time level: a level can only be dense up to 2^24 entries (level 4), finer ones are always hashed.
+template <bool NC = true, int LVL = 0>
 __device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t size_mask, uint32_t res,
                                                float scale, bool dense, float x, float y, float z) {
     float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
@@ -97,36 +101,50 @@ __device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t si
         g[d] = (uint32_t)(int)fl;
         p[d] -= fl;
     }
+    const float fx[2] = {1.0f - p[0], p[0]}, fy[2] = {1.0f - p[1], p[1]}, fz[2] = {1.0f - p[2], p[2]};
+    const float wxy[4] = {fx[0] * fy[0], fx[1] * fy[0], fx[0] * fy[1], fx[1] * fy[1]};
+    uint32_t idx[8];
+    if (LVL < 5 && dense) {
+        const uint32_t r2 = res * res;
+        const uint32_t cy[2] = {g[1] * res, g[1] * res + res}, cz[2] = {g[2] * r2, g[2] * r2 + r2};
+#pragma unroll
+        for (int c = 0; c < 8; ++c) idx[c] = (g[0] + (c & 1) + cy[(c >> 1) & 1] + cz[c >> 2]) & size_mask;
+    } else {
+        const uint32_t cx[2] = {g[0] & size_mask, (g[0] + 1) & size_mask};
+        const uint32_t hy = g[1] * 2654435761u, hz = g[2] * 805459861u;
+        const uint32_t cy[2] = {hy & size_mask, (hy + 2654435761u) & size_mask};
+        const uint32_t cz[2] = {hz & size_mask, (hz + 805459861u) & size_mask};
+#pragma unroll
+        for (int c = 0; c < 8; ++c) idx[c] = cx[c & 1] ^ cy[(c >> 1) & 1] ^ cz[c >> 2];
+    }
     __half2 acc = __float2half2_rn(0.0f);
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-        float w = 1.0f;
-        uint32_t gl[3];
-#pragma unroll
-        for (int d = 0; d < 3; ++d) {
-            if (c & (1 << d)) { w *= p[d]; gl[d] = g[d] + 1; } else { w *= 1.0f - p[d]; gl[d] = g[d]; }
-        }
-        uint32_t idx;
-        if (dense) idx = gl[0] + gl[1] * res + gl[2] * res * res;
-        else idx = gl[0] ^ (gl[1] * 2654435761u) ^ (gl[2] * 805459861u);
+        const float w = wxy[c & 3] * fz[c >> 2];
         __half2 v;
-        if constexpr (NC) v = __ldg(table + (idx & size_mask));
-        else v = table[idx & size_mask];
+        if constexpr (NC) v = __ldg(table + idx[c]);
+        else v = table[idx[c]];
         acc = __hfma2(__float2half2_rn(w), v, acc);
     }
     return *reinterpret_cast<uint32_t*>(&acc);
+}
+
+// Levels [L0, L1) -> e[L0 .. L1), the level index a compile-time constant.
+template <bool NC, int L0, int L1, int N>
+__device__ __forceinline__ void grid_levels(const float (&q)[15], const __half2* grid, const GridMeta& gm, uint32_t (&e)[N]) {
+    if constexpr (L0 < L1) {
+        const uint32_t size = gm.offset[L0 + 1] - gm.offset[L0];
+        e[L0] = grid_level<NC, L0>(grid + gm.offset[L0], size - 1, gm.resolution[L0], gm.scale[L0], (gm.dense_mask >> L0) & 1,
+                                   q[0], q[1], q[2]);
+        grid_levels<NC, L0 + 1, L1>(q, grid, gm, e);
+    }
 }
 
 // Hash config: 15 raw floats -> 64 fp16 features packed as 32 half2 words. Level tables are powers of two
 // (NRCNetworkConfigs.h:98-104: 16^3 = 4096 entries at level 0, 2^log2_hashmap_size above), so `% size` is a mask.
 __device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2* __restrict__ grid,
                                             const GridMeta& gm, uint32_t (&e)[32]) {
-#pragma unroll
-    for (int l = 0; l < 16; ++l) {
-        const uint32_t size = gm.offset[l + 1] - gm.offset[l];
-        e[l] = grid_level(grid + gm.offset[l], size - 1, gm.resolution[l], gm.scale[l], (gm.dense_mask >> l) & 1, q[0],
-                          q[1], q[2]);
-    }
+    grid_levels<true, 0, 16>(q, grid, gm, e);
 #pragma unroll
     for (int d = 0; d < 6; ++d) {
         float y[4];
@@ -177,12 +195,7 @@ template <int HF>
 __device__ __forceinline__ void encode_hash_half(const float (&q)[15], const __half2* grid,
                                                  const GridMeta& gm, uint32_t (&e)[16]) {
     if constexpr (HF == 0) {
-#pragma unroll
-        for (int l = 0; l < 16; ++l) {
-            const uint32_t size = gm.offset[l + 1] - gm.offset[l];
-            e[l] = grid_level<false>(grid + gm.offset[l], size - 1, gm.resolution[l], gm.scale[l],
-                                     (gm.dense_mask >> l) & 1, q[0], q[1], q[2]);
-        }
+        grid_levels<false, 0, 16>(q, grid, gm, e);
     } else {
 #pragma unroll
         for (int d = 0; d < 6; ++d) {
