@@ -75,15 +75,21 @@ static void make_layout(Net* n) {
         for (int l = 0; l < 16; ++l) {  // grid.h:692-723
             const float scale = exp2f((float)l) * 16.0f - 1.0f;  // common_device.h:856-861
             const uint32_t res = (uint32_t)ceilf(scale) + 1;
-            const double dense = (double)res * res * res;
+            const double dense = (double)res * res * res;   // params_in_level before the cap (grid.h:703-707)
             const uint32_t cap = 1u << n->log2_hashmap;
             uint32_t size = dense > (double)cap ? cap : (uint32_t)dense;
             size = (size + 7u) / 8u * 8u;
             if (size > cap) size = cap;
             n->gm.offset[l] = off;
-            n->gm.resolution[l] = res;
             n->gm.scale[l] = scale;
-            if (dense <= (double)size) n->gm.dense_mask |= 1u << l;
+            // grid_index (common_device.h:691-707), literally, in uint32: which dimensions enter the linear index with
+            // which stride, and whether the level ends up hashed.  res^2 wraps to 0 for res >= 2^16, so fine levels of a
+            // table with >= res entries leave the loop with stride 0 <= size: NOT hashed, index = x + y*res.
+            uint32_t stride = 1, st[3] = {0, 0, 0};
+            for (int dim = 0; dim < 3 && stride <= size; ++dim) { st[dim] = stride; stride *= res; }
+            n->gm.stride_y[l] = st[1];
+            n->gm.stride_z[l] = st[2];
+            if (!(size < stride)) n->gm.dense_mask |= 1u << l;
             off += size;
         }
         n->gm.offset[16] = off;

@@ -18,9 +18,10 @@ namespace nrcb {
 // Layout of the multiresolution hash grid (grid.h:692-723), filled by the host (nrc_b200.cu).
 struct GridMeta {
     uint32_t offset[17];   // cumulative entry offsets (entries of 2 fp16 features)
-    uint32_t resolution[16];
+    uint32_t stride_y[16]; // index = x + y*stride_y + z*stride_z (mod 2^32) on the levels that are not hashed: the strides the
+    uint32_t stride_z[16]; // reference's grid_index loop ends up with, INCLUDING its uint32 wrap (common_device.h:691-707)
     float scale[16];
-    uint32_t dense_mask;   // bit l set: level l is indexed densely (res^3 <= table size)
+    uint32_t dense_mask;   // bit l set: level l is NOT hashed (res^3 <= table size, or the stride wrapped to 0)
 };
 
 // Wrapped quartic-kernel CDF sum  c(d) + c(d-1) + c(d+1)  with  c(t) = clamp(P(4t) + 0.5, 0, 1).
@@ -89,9 +90,11 @@ __device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t 
 // table later in the same launch.
 // The per-axis index terms are computed once per level (2 values per axis, already masked: & distributes over ^), so a
 // corner costs one 3-input LOP3 (hashed) or one IADD3 + mask (dense) instead of two multiplies and two xors.
-// LVL is the compile-time level: a level can only be dense up to 2^24 entries (level 4), finer ones are always hashed.
+// Which levels are hashed follows the reference's grid_index literally (GridMeta, filled by the host): besides the truly
+// dense coarse levels, fine levels whose stride res^2 wraps to 0 in uint32 (res >= 2^16 with a table >= res entries) come
+// out of that loop un-hashed as x + y*res.
 template <bool NC = true, int LVL = 0>
-__device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t size_mask, uint32_t res,
+__device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t size_mask, uint32_t sy, uint32_t sz,
                                                float scale, bool dense, float x, float y, float z) {
     float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
     uint32_t g[3];
@@ -104,9 +107,8 @@ __device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t si
     const float fx[2] = {1.0f - p[0], p[0]}, fy[2] = {1.0f - p[1], p[1]}, fz[2] = {1.0f - p[2], p[2]};
     const float wxy[4] = {fx[0] * fy[0], fx[1] * fy[0], fx[0] * fy[1], fx[1] * fy[1]};
     uint32_t idx[8];
-    if (LVL < 5 && dense) {
-        const uint32_t r2 = res * res;
-        const uint32_t cy[2] = {g[1] * res, g[1] * res + res}, cz[2] = {g[2] * r2, g[2] * r2 + r2};
+    if (dense) {
+        const uint32_t cy[2] = {g[1] * sy, g[1] * sy + sy}, cz[2] = {g[2] * sz, g[2] * sz + sz};
 #pragma unroll
         for (int c = 0; c < 8; ++c) idx[c] = (g[0] + (c & 1) + cy[(c >> 1) & 1] + cz[c >> 2]) & size_mask;
     } else {
@@ -134,7 +136,7 @@ template <bool NC, int L0, int L1, int N>
 __device__ __forceinline__ void grid_levels(const float (&q)[15], const __half2* grid, const GridMeta& gm, uint32_t (&e)[N]) {
     if constexpr (L0 < L1) {
         const uint32_t size = gm.offset[L0 + 1] - gm.offset[L0];
-        e[L0] = grid_level<NC, L0>(grid + gm.offset[L0], size - 1, gm.resolution[L0], gm.scale[L0], (gm.dense_mask >> L0) & 1,
+        e[L0] = grid_level<NC, L0>(grid + gm.offset[L0], size - 1, gm.stride_y[L0], gm.stride_z[L0], gm.scale[L0], (gm.dense_mask >> L0) & 1,
                                    q[0], q[1], q[2]);
         grid_levels<NC, L0 + 1, L1>(q, grid, gm, e);
     }

@@ -425,7 +425,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 const int lv = hf * 8 + j;
                 const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * j])));
                 const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * j + 1])));
-                const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], res = gm.resolution[lv];
+                const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
                 float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
                 const bool active = g0 != 0.0f || g1 != 0.0f;
@@ -455,7 +455,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     for (int d = 0; d < 3; ++d) {
                         if (c & (1 << d)) { wgt *= p[d]; cc[d] = gp[d] + 1; } else { wgt *= 1.0f - p[d]; cc[d] = gp[d]; }
                     }
-                    const uint32_t idx = (dense ? cc[0] + cc[1] * res + cc[2] * res * res
+                    const uint32_t idx = (dense ? cc[0] + cc[1] * sy + cc[2] * sz
                                                 : cc[0] ^ (cc[1] * 2654435761u) ^ (cc[2] * 805459861u)) & (size - 1);
                     const float wh = __half2float(__float2half_rn(wgt));   // (GRAD_T)weight, grid.h:254
                     float v0 = active ? wh * g0 : 0.0f, v1 = active ? wh * g1 : 0.0f;

@@ -106,3 +106,14 @@ def test_infer_host_buffers(pkg, orc, synth):
     net.destroy()
     idx = np.random.default_rng(0).choice(n, 20000, replace=False)
     _check(out[idx], orc.infer(orc.make_spec(0), w16, q[idx]))
+
+
+@pytest.mark.parametrize("log2", [14, 18, 21])
+def test_infer_hash_table_sizes(pkg, orc, synth, log2):
+    """BASELINE.json configs[4] sweeps the HashGrid table size: the set of densely indexed levels changes with it
+    (res^3 <= 2^log2: level 0 only at 2^14; levels 0-2 at 2^18; levels 0-3 at 2^21), and so does the lookup code path."""
+    q = synth.uniform_queries(4096, seed=log2)        # positions over the whole unit cube: every level's index range is hit
+    got, ref = _run(pkg, orc, pkg.HASH, q, log2=log2)
+    _check(got, ref)
+    got, ref = _run(pkg, orc, pkg.HASH, synth.cornell_queries(4096, seed=log2), log2=log2)   # negative coordinates
+    _check(got, ref)

@@ -185,3 +185,30 @@ def test_train_batches_is_the_loop_of_train_calls(pkg, synth, enc):
     oa, ob = torch.empty(4096, 3, device="cuda"), torch.empty(4096, 3, device="cuda")
     a.infer(probe, oa, 4096); b.infer(probe, ob, 4096)
     assert torch.equal(oa, ob)
+
+
+@pytest.mark.parametrize("log2", [14, 18])
+def test_hash_single_step_other_table_sizes(pkg, orc, synth, log2):
+    """One optimizer step of the Hash configuration with a smaller / larger table than the default 2^15 (dense levels 0 /
+    0-2): loss and the matrix gradients against the oracle, grid gradient through its sum and its support."""
+    import torch
+    net = pkg.Network()
+    net.init(0, 1, log2_hashmap_size=log2, seed=7)
+    tr = orc.Trainer(1, log2_hashmap=log2)
+    master = net.get_params(pkg.PARAMS_MASTER_F32)
+    nm = net.n_params()[1]
+    master[nm:] = np.random.default_rng(3).uniform(-0.1, 0.1, master.size - nm).astype(np.float32)
+    net.load_master(master)
+    tr.set_master(master)
+    q, t = _batch(synth, 33)
+    loss = net.train(torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda(), want_loss=True)
+    loss_ref = tr.train_step(q, t)
+    assert abs(loss - loss_ref) <= 1e-3 * abs(loss_ref), (loss, loss_ref)
+    g, g_ref = net.get_params(pkg.PARAMS_GRAD_F16).astype(np.float32), tr.grads.astype(np.float32)
+    for sl in _layer_slices(1):
+        assert np.abs(g[sl] - g_ref[sl]).max() <= 1e-2 * np.abs(g_ref[sl]).max()
+    gg, gr = g[nm:].astype(np.float64), g_ref[nm:].astype(np.float64)
+    assert abs(np.abs(gg).sum() - np.abs(gr).sum()) <= 5e-3 * np.abs(gr).sum()
+    assert abs(int((gg != 0).sum()) - int((gr != 0).sum())) <= 2e-3 * int((gr != 0).sum()) + 4
+    tr.close()
+    net.destroy()

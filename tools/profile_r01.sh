@@ -2,7 +2,7 @@
 # ncu evidence for one encoding: launch list + full captures of the query kernel and the training tile kernel.
 # usage (on the GPU box, via gpurun): bash tools/profile_r01.sh frequency|hash <tag>
 ENC=${1:-frequency}; TAG=${2:-r01}
-CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --e2e-steps 1 --encoding $ENC"
+CMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-other-encoding --e2e-steps 1 --encoding $ENC"
 $CMD > gpurun_out/${TAG}_plain_${ENC}.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/${TAG}_plain_${ENC}.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_launches_${ENC}.csv $CMD > /dev/null 2>&1
 ncu --set full --clock-control none --import-source on -k regex:nrc_infer -s 3 -c 1 -f -o gpurun_out/${TAG}_infer_${ENC} $CMD > /dev/null 2>&1
