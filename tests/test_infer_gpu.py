@@ -117,3 +117,21 @@ def test_infer_hash_table_sizes(pkg, orc, synth, log2):
     _check(got, ref)
     got, ref = _run(pkg, orc, pkg.HASH, synth.cornell_queries(4096, seed=log2), log2=log2)   # negative coordinates
     _check(got, ref)
+
+
+@pytest.mark.parametrize("enc", [0, 1])
+def test_infer_wide_range_inputs(pkg, orc, enc):
+    """Inputs far outside the renderer's ranges (positions in [-3, 4], angles in [-12, 12], roughness in [-2, 3], albedos up
+    to 8, exact zeros / ones / bin edges): the folded tri-wave and wrapped one-blob forms and the unsigned grid coordinates
+    must still agree with the oracle's literal restatement."""
+    rng = np.random.default_rng(17 + enc)
+    n = 8192
+    q = np.empty((n, 15), dtype=np.float32)
+    q[:, 0:3] = rng.uniform(-3.0, 4.0, (n, 3))
+    q[:, 3:7] = rng.uniform(-12.0, 12.0, (n, 4))
+    q[:, 7:9] = rng.uniform(-2.0, 3.0, (n, 2))
+    q[:, 9:15] = rng.uniform(0.0, 8.0, (n, 6))
+    special = np.array([0.0, 1.0, -1.0, 0.25, 0.5, 0.75, -0.25, 1.25, 2.0, -0.0, 1e-30, -1e-30, 0.125, 0.375, 3.0, -3.0], dtype=np.float32)
+    q[:256] = special[rng.integers(0, special.size, (256, 15))]
+    got, ref = _run(pkg, orc, enc, q, weights_scale=0.25)
+    _check(got, ref)
