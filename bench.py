@@ -52,6 +52,9 @@ def parse_args():
     ap.add_argument("--per-batch-launch", action="store_true",
                     help="one nrc_b200_train launch per batch (the reference's call pattern) instead of nrc_b200_train_batches")
     ap.add_argument("--no-other-encoding", action="store_true", help="skip the short run of the other encoding")
+    ap.add_argument("--shard-frame", type=int, default=0, metavar="TOTAL",
+                    help="strong scaling (BASELINE.json configs[3]): ONE frame of TOTAL queries (4K: 8424000) batch-sharded over the "
+                         "ranks, 16384-sample training batches split across the ranks; default: every rank owns a full frame")
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--dp", choices=["fused", "nccl"], default="fused",
@@ -232,6 +235,12 @@ def run_ours(args, enc):
     synth = entry.load_package_synthetic()
     nq = args.queries
     n_train = NUM_BATCHES * BATCH_SIZE
+    strong = args.shard_frame > 0
+    train_local = BATCH_SIZE                     # samples of each training batch this rank processes
+    if strong:                                   # one frame for the whole job: contiguous tile-aligned shard per rank
+        lo, hi = importlib.import_module("nrc_b200.dist").shard_range(args.shard_frame, rank, world) if world > 1 else (0, args.shard_frame)
+        nq = hi - lo
+        train_local = BATCH_SIZE // world
 
     # ---- inputs: host (pinned) + device-resident copies
     q_np, tq_np, tt_np = make_inputs(synth, nq, rank, args.query_order)
@@ -254,8 +263,10 @@ def run_ours(args, enc):
         ts = t_ptr_t + b * BATCH_SIZE * 12
         if world == 1:
             return net.train(qs, ts, sp, want_loss=want_loss)
-        # shard -> gradient (normalised by the global batch) -> NCCL all-reduce over NVLink -> Adam+EMA
-        return dp.train(qs, ts, BATCH_SIZE, sp, want_loss=want_loss)
+        # shard -> gradient (normalised by the global batch) -> all-reduce over NVLink -> Adam+EMA
+        # (strong scaling: this rank's slice of the SAME 16384-sample batch)
+        off = rank * train_local if strong else 0
+        return dp.train(qs + off * 60, ts + off * 12, train_local, sp, want_loss=want_loss)
 
     q_ptr_t, t_ptr_t = tq_d.data_ptr(), tt_d.data_ptr()
     ev_inf = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -299,7 +310,8 @@ def run_ours(args, enc):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     ms_step = ms_total / args.steps
-    value = world * (nq + n_train) / (ms_step * 1e-3)
+    total_units = (args.shard_frame + n_train) if strong else world * (nq + n_train)
+    value = total_units / (ms_step * 1e-3)
 
     # ---- e2e: host buffers through the C ABI (H2D of queries / batches and D2H of radiance + loss inside)
     def update_host():
@@ -329,7 +341,7 @@ def run_ours(args, enc):
         t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e = {"value": world * (nq + n_train) / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
+    e2e = {"value": total_units / e2e_s, "unit": UNIT, "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
            "h2d_bytes_per_step": nq * 60 + n_train * 72, "d2h_bytes_per_step": nq * 12 + 4,
            "timing": "host wall clock between device synchronisations, max over ranks"}
 
@@ -407,16 +419,19 @@ def run_ours(args, enc):
                 "traffic": TRAFFIC_BYTES.get((enc, nq))}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16",
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f16",
             "data": "synthetic",
-            "config": {"workload": workload_name(enc, nq), "queries_per_gpu": nq, "train_samples_per_gpu": n_train,
+            "config": {"workload": (f"ONE frame of {args.shard_frame} queries batch-sharded over {world} GPUs + {NUM_BATCHES}x{BATCH_SIZE} "
+                                    f"training samples split across them, {'Frequency' if enc == 0 else 'Hash'} encoding, 5x64 ReLU MLP")
+                                   if strong else workload_name(enc, nq),
+                       "queries_per_gpu": nq, "train_samples_per_gpu": NUM_BATCHES * train_local if world > 1 else n_train,
                        "parallelism": (f"dp{world} ({args.dp} all-reduce)") if world > 1 else "single",
                        "query_order": ("pixel-ordered primary hits of a pinhole camera in the Cornell box + incoherent "
                                        "tile tails" if args.query_order == "frame" else
                                        "independent random surface points (incoherent worst case for the hash grid)"),
                        "l2": f"inputs larger than L2 ({nq * 60 / 1e6:.0f} MB of queries per step vs 126 MB L2)"},
-            "queries_per_s": world * nq / (t_inf_ms * 1e-3),
-            "train_samples_per_s": world * n_train / max((ms_step - t_inf_ms) * 1e-3, 1e-9),
+            "queries_per_s": (args.shard_frame if strong else world * nq) / (t_inf_ms * 1e-3),
+            "train_samples_per_s": (n_train if strong else world * n_train) / max((ms_step - t_inf_ms) * 1e-3, 1e-9),
             "ms_infer": t_inf_ms, "ms_train_4_steps": ms_step - t_inf_ms,
             "frame_driver_ms": frame_ms, "other_encoding": other, "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline}
     net.destroy()
