@@ -19,6 +19,7 @@
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
+#include <type_traits>
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
 #include "nrc_frame.cuh"
@@ -124,6 +125,12 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
 // in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
 __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s) {
+    // The bias-corrected learning rate depends on the parameter's own step count only; almost every touched entry has
+    // been touched in every step so far, so the two powf of that common count are evaluated once per thread.
+    // (evaluated after the first group of loads has been issued, so it overlaps their latency)
+    const uint32_t common = a.dp_step + s;
+    float lr_common = 0.0f;
+    bool have_lr = false;
     for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 8 * kTrainThreads) {
         float4 g[2], w[2], m1[2], m2[2];
         uint4 st[2];
@@ -143,6 +150,10 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                 em[u] = *reinterpret_cast<const uint2*>(a.ema + i);
                 pr[u] = *reinterpret_cast<const uint2*>(a.params + i);
             }
+        }
+        if (!have_lr) {
+            lr_common = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)common)) / (1.0f - powf(a.beta1, (float)common)));
+            have_lr = true;
         }
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
@@ -164,7 +175,8 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                     av[c] = a.beta1 * av[c] + (1.0f - a.beta1) * gradient;
                     bv[c] = a.beta2 * bv[c] + (1.0f - a.beta2) * (gradient * gradient);
                     const uint32_t cur = ++sv[c];
-                    const float lr = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+                    const float lr = cur == common ? lr_common
+                                                   : a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
                     const float eff = fminf(fmaxf(lr / (sqrtf(bv[c]) + a.eps), 0.0f), 3.402823466e+38f);
                     wv[c] = wv[c] - eff * av[c];
                     pv[c] = __float2half_rn(wv[c]);
@@ -191,6 +203,9 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
 
 #ifndef NRCB_SCATTER_AGG
 #define NRCB_SCATTER_AGG 1
+#endif
+#ifndef NRCB_AGG_LEVELS
+#define NRCB_AGG_LEVELS 8     // coarsest levels whose scatter is pre-aggregated per tile in shared memory
 #endif
 // ---------------------------------------------------------------- the step kernel
 template <int ENC, bool MULTI>   // MULTI: a.n_steps optimizer steps in this launch (separate instantiation: the loop costs the
@@ -402,38 +417,40 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         stamp(3);
         if (warp == 0 && lane == 0) a.loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
         if constexpr (ENC == 1) {
-            // Grid gradient scatter (grid.h:252-255,301-319): half hf handles levels 8*hf .. 8*hf+7 (columns 16*hf ..).
-            // The coarse levels (half 0) are pre-aggregated per tile in a shared-memory table keyed by the entry index:
+            // Grid gradient scatter (grid.h:252-255,301-319).  Both threads of a sample walk all 16 levels; half hf takes the
+            // four corners with dz = hf, so the halves finish together (with levels split 8 / 8 the half that owned the
+            // aggregated coarse levels took 21 us, the other 9).
+            // The kAggLevels coarsest levels are pre-aggregated per tile in a shared-memory table keyed by the entry index:
             // a concentrated scene (the Cornell box spans 0.1 of the unit cube) sends all 16384 x 8 corner updates of a
             // coarse level to a few dozen entries, which serialises global atomics in L2 (33 us measured).  After the
             // aggregation every CTA issues one global red per DISTINCT entry it touched.
             constexpr uint32_t kSlots = 2048, kEmpty = 0xFFFFFFFFu;
+            constexpr int kAggLevels = NRCB_SCATTER_AGG ? NRCB_AGG_LEVELS : 0;
             uint32_t* s_tag = reinterpret_cast<uint32_t*>(smem + L::kH);            // [kSlots]   (activations are dead now)
             int* s_acc = reinterpret_cast<int*>(smem + L::kH + kSlots * 4);          // [kSlots][2] fixed point
             uint32_t* s_max = reinterpret_cast<uint32_t*>(smem + L::kH + kSlots * 12); // tile maximum of |dL/dy| (float bits)
-            const int htid = qd * 32 + lane;                                          // 0..127 inside the half
-            if (hf == 0) {
-                for (uint32_t sl = htid; sl < kSlots; sl += 128) { s_tag[sl] = kEmpty; s_acc[2 * sl] = 0; s_acc[2 * sl + 1] = 0; }
-                if (htid == 0) *s_max = 0;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-            }
-            uint32_t v[16];
-            tmem_ld16(tq + kAcc + hf * 16, v);
+            const uint32_t wtid = warp * 32 + lane;                                   // 0..255 over the 8 worker warps
+            auto workers_sync = [] { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+            for (uint32_t sl = wtid; sl < kSlots; sl += 256) { s_tag[sl] = kEmpty; s_acc[2 * sl] = 0; s_acc[2 * sl + 1] = 0; }
+            if (wtid == 0) *s_max = 0;
+            workers_sync();
+            uint32_t v[32];
+            tmem_ld32(tq + kAcc, v);
             tmem_wait_ld();
-#pragma unroll 1
-            for (int j = 0; j < 8; ++j) {
-                const int lv = hf * 8 + j;
-                const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * j])));
-                const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * j + 1])));
+            auto level = [&](auto LV) {
+                constexpr int lv = decltype(LV)::value;
+                constexpr bool agg = lv < kAggLevels;
+                const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv])));
+                const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv + 1])));
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
                 float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
                 const bool active = g0 != 0.0f || g1 != 0.0f;
                 float S = 0.0f, Sinv = 0.0f;
-                if (hf == 0 && NRCB_SCATTER_AGG) {   // common scale of this level for the whole tile
+                if constexpr (agg) {   // common scale of this level for the whole tile
                     const uint32_t mx = __reduce_max_sync(0xffffffffu, max(__float_as_uint(fabsf(g0)), __float_as_uint(fabsf(g1))));
-                    if (lane == 0) atomicMax(s_max, mx);
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (lane == 0 && hf == 0) atomicMax(s_max, mx);
+                    workers_sync();
                     const uint32_t eb = max(*s_max >> 23, 24u);
                     S = __uint_as_float((273u - eb) << 23);
                     Sinv = __uint_as_float((eb - 19u) << 23);
@@ -447,52 +464,55 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     gp[d] = (uint32_t)(int)fl;
                     p[d] -= fl;
                 }
+                const float fz = hf ? p[2] : 1.0f - p[2];
+                const uint32_t cz = gp[2] + hf;
 #pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    float wgt = 1.0f;
-                    uint32_t cc[3];
-#pragma unroll
-                    for (int d = 0; d < 3; ++d) {
-                        if (c & (1 << d)) { wgt *= p[d]; cc[d] = gp[d] + 1; } else { wgt *= 1.0f - p[d]; cc[d] = gp[d]; }
-                    }
-                    const uint32_t idx = (dense ? cc[0] + cc[1] * sy + cc[2] * sz
-                                                : cc[0] ^ (cc[1] * 2654435761u) ^ (cc[2] * 805459861u)) & (size - 1);
+                for (int c = 0; c < 4; ++c) {
+                    const float wgt = (((c & 1) ? p[0] : 1.0f - p[0]) * ((c & 2) ? p[1] : 1.0f - p[1])) * fz;
+                    const uint32_t cx = gp[0] + (c & 1), cy = gp[1] + (c >> 1);
+                    const uint32_t idx = (dense ? cx + cy * sy + cz * sz
+                                                : cx ^ (cy * 2654435761u) ^ (cz * 805459861u)) & (size - 1);
                     const float wh = __half2float(__float2half_rn(wgt));   // (GRAD_T)weight, grid.h:254
-                    float v0 = active ? wh * g0 : 0.0f, v1 = active ? wh * g1 : 0.0f;
-                    if (hf != 0 || !NRCB_SCATTER_AGG) {
-                        if (active) asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
-                        continue;
-                    }
-                    // CTA-level aggregation in a shared-memory table of FIXED-POINT accumulators: 32-bit integer atomics are
-                    // native in shared memory (ATOMS.ADD; float / 64-bit adds compile to CAS spin loops that collapse
-                    // under same-address conflicts).  Scale: 20 bits below the largest |dL/dy| of the tile at this level,
-                    // 1024 terms of headroom.
+                    const float v0 = wh * g0, v1 = wh * g1;
                     if (!active) continue;
-                    const uint32_t sl = idx & (kSlots - 1);
-                    const uint32_t old = atomicCAS(&s_tag[sl], kEmpty, idx);
-                    if (old == kEmpty || old == idx) {
-                        atomicAdd(&s_acc[2 * sl], __float2int_rn(v0 * S));
-                        atomicAdd(&s_acc[2 * sl + 1], __float2int_rn(v1 * S));
-                    } else {
+                    if constexpr (!agg) {
                         asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
+                    } else {
+                        // CTA-level aggregation in a shared-memory table of FIXED-POINT accumulators: 32-bit integer atomics
+                        // are native in shared memory (ATOMS.ADD; float / 64-bit adds compile to CAS spin loops that collapse
+                        // under same-address conflicts).  Scale: 20 bits below the largest |dL/dy| of the tile at this level,
+                        // 1024 terms of headroom.
+                        const uint32_t sl = idx & (kSlots - 1);
+                        const uint32_t old = atomicCAS(&s_tag[sl], kEmpty, idx);
+                        if (old == kEmpty || old == idx) {
+                            atomicAdd(&s_acc[2 * sl], __float2int_rn(v0 * S));
+                            atomicAdd(&s_acc[2 * sl + 1], __float2int_rn(v1 * S));
+                        } else {
+                            asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
+                        }
                     }
                 }
-                if (hf == 0) {   // flush the table of this level: one global red per distinct entry
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    for (uint32_t sl = htid; sl < kSlots; sl += 128) {
+                if constexpr (agg) {   // flush the table of this level: one global red per distinct entry
+                    workers_sync();
+                    for (uint32_t sl = wtid; sl < kSlots; sl += 256) {
                         const uint32_t tg_ = s_tag[sl];
                         if (tg_ != kEmpty) {
                             asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * tg_), "f"((float)s_acc[2 * sl] * Sinv), "f"((float)s_acc[2 * sl + 1] * Sinv) : "memory");
                             s_tag[sl] = kEmpty; s_acc[2 * sl] = 0; s_acc[2 * sl + 1] = 0;
                         }
                     }
-                    if (htid == 0) *s_max = 0;
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (wtid == 0) *s_max = 0;
+                    workers_sync();
                 }
-#ifdef NRCB_DEBUG_LEVELS
-                if (a.timeline && tid == 0 && s == 0) a.timeline[tile * 8 + j] = clock64();
-#endif
-            }
+            };
+            level(std::integral_constant<int, 0>{}); level(std::integral_constant<int, 1>{});
+            level(std::integral_constant<int, 2>{}); level(std::integral_constant<int, 3>{});
+            level(std::integral_constant<int, 4>{}); level(std::integral_constant<int, 5>{});
+            level(std::integral_constant<int, 6>{}); level(std::integral_constant<int, 7>{});
+            level(std::integral_constant<int, 8>{}); level(std::integral_constant<int, 9>{});
+            level(std::integral_constant<int, 10>{}); level(std::integral_constant<int, 11>{});
+            level(std::integral_constant<int, 12>{}); level(std::integral_constant<int, 13>{});
+            level(std::integral_constant<int, 14>{}); level(std::integral_constant<int, 15>{});
         }
         if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
         // per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.
