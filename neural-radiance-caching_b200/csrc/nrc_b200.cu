@@ -411,7 +411,7 @@ int nrc_b200_train_grad(nrc_b200_handle h, const float* q, const float* t, uint3
     if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
     if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
         return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
-    h->barrier_total += n_local / 128;
+    h->barrier_total += train_grid(n_local);
     CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/0), h->gm, h->stream));
     h->launches += 1;
     h->pending_tiles = n_local / 128;
@@ -515,7 +515,7 @@ int nrc_b200_train_dp(nrc_b200_handle h, const float* q, const float* t, uint32_
     if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
         return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
     h->step += 1;
-    h->barrier_total += n_local / 128;
+    h->barrier_total += train_grid(n_local);
     CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/1), h->gm, h->stream));
     h->launches += 1;
     h->pending_tiles = 0;

@@ -63,6 +63,9 @@ struct TrainArgs {
     uint32_t* xflag[8];
 };
 constexpr int kMaxDpRanks = 8;
+// CTAs of a step launch: one per 128-sample tile, but never fewer than 128 -- short data-parallel shards keep the gradient
+// reduction / optimizer phase 128 slices wide (the extra CTAs skip phase 1).  The grid barrier counts this many arrivals.
+inline uint32_t train_grid(uint32_t n_local) { const uint32_t t = n_local / 128; return t < 128 ? 128 : t; }
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream);
 
 // Adam + EMA from an already reduced fp32 gradient (after a data-parallel all-reduce); clears grid_grad.

@@ -124,7 +124,10 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
 
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
 // in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
-__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s) {
+// load_g(j) returns the reduced fp32 gradient of grid parameters j..j+3; clear: zero the scatter accumulator behind it.
+template <class LoadG>
+__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s,
+                                                LoadG load_g, bool clear) {
     // The bias-corrected learning rate depends on the parameter's own step count only; almost every touched entry has
     // been touched in every step so far, so the two powf of that common count are evaluated once per thread.
     // (evaluated after the first group of loads has been issued, so it overlaps their latency)
@@ -142,7 +145,7 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
             live[u] = j < ghi;
             if (live[u]) {
                 const uint32_t i = base + j;
-                g[u] = __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j));
+                g[u] = load_g(j);
                 w[u] = *reinterpret_cast<const float4*>(a.master + i);
                 m1[u] = *reinterpret_cast<const float4*>(a.m1 + i);
                 m2[u] = *reinterpret_cast<const float4*>(a.m2 + i);
@@ -195,7 +198,7 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                 *reinterpret_cast<uint4*>(a.steps + i) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
                 *reinterpret_cast<uint2*>(a.params + i) = *reinterpret_cast<uint2*>(pv);
             }
-            if (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f)   // also gradients that round to 0 in fp16
+            if (clear && (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f))   // also gradients that round to 0 in fp16
                 *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         }
     }
@@ -226,7 +229,9 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t tile = blockIdx.x;
-    const uint32_t n_tiles = gridDim.x;
+    const uint32_t n_tiles = gridDim.x;              // CTAs = gradient slices of phase 3 (>= data tiles)
+    const uint32_t n_data = a.n_local / kTT;         // 128-sample tiles of this launch: CTAs [0, n_data) run phase 1
+    const bool has_tile = tile < n_data;
     const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0 && a.perm_n == 0;   // bulk copy needs a contiguous tile
     uint32_t s = 0;                 // optimizer step within this launch
     auto stamp = [&](int slot) { if (a.timeline && tid == 0 && s == 0) a.timeline[tile * 8 + slot] = clock64(); };
@@ -247,7 +252,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
 
   for (s = 0; s < n_steps; ++s) {
     const uint32_t first = s * a.n_local + tile * kTT;   // first sample of this tile in this step
-    if (tid == 0) {
+    if (tid == 0 && has_tile) {
         // s > 0: the weight image was rewritten with generic stores by every CTA in the previous step; the grid barrier
         // ordered them, this makes them visible to the bulk copy (async proxy).
         if (s > 0) asm volatile("fence.proxy.async;" ::: "memory");
@@ -259,7 +264,9 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         }
     }
 
-    if (warp == kWorkerWarps) {
+    if (!has_tile) {
+        // a slice-only CTA (short data-parallel shard): nothing to do before the grid barrier
+    } else if (warp == kWorkerWarps) {
         // ======================= MMA issuer =======================
         const bool leader = elect_one();
         uint32_t ph = 0;
@@ -575,19 +582,19 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         const uint32_t lo = min((uint32_t)NMLP, tile * S), hi = min((uint32_t)NMLP, lo + S);
         const uint32_t ncol4 = (hi - lo) >> 2;                             // NMLP % 4 == 0 -> whole float4 columns
         float4* scratch = reinterpret_cast<float4*>(smem + L::kScratch);   // [groups][ncol4]
-        const uint32_t groups = ncol4 == 0 ? 0 : (ncol4 >= (uint32_t)kTrainThreads ? 1 : min((uint32_t)kTrainThreads / ncol4, n_tiles));
+        const uint32_t groups = ncol4 == 0 ? 0 : (ncol4 >= (uint32_t)kTrainThreads ? 1 : min((uint32_t)kTrainThreads / ncol4, n_data));
         for (uint32_t w = tid; w < groups * ncol4; w += kTrainThreads) {   // one pass when the batch has >= 20 tiles
             const uint32_t g = w / ncol4, c4 = w - g * ncol4;
             const float* src = a.partials + lo + 4 * c4;
             float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
             // batches of 8 independent L2 loads in flight (a dependent chain of ~0.4 us L2 hits otherwise), summed in
             // increasing tile order
-            for (uint32_t t0 = g; t0 < n_tiles; t0 += 8 * groups) {
+            for (uint32_t t0 = g; t0 < n_data; t0 += 8 * groups) {
                 float4 v[8];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
                     const uint32_t t = t0 + u * groups;
-                    v[u] = t < n_tiles ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)t * NMLP)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    v[u] = t < n_data ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)t * NMLP)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 }
 #pragma unroll
                 for (int u = 0; u < 8; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
@@ -613,13 +620,13 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 if (a.apply) adam_ema_param(a, lo + j, g, E, s);
             }
             if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
-                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s);
+                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) { return __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j)); }, true);
                 else
                     for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) a.grad_f32[NMLP + j] = __ldcg(a.grid_grad + j);
             }
             if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
                 float l = 0.0f;
-                for (uint32_t t = lane; t < n_tiles; t += 32) l += __ldcg(a.loss_partials + t);
+                for (uint32_t t = lane; t < n_data; t += 32) l += __ldcg(a.loss_partials + t);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
                 if (lane == 0) a.loss_out[s] = l;
@@ -643,7 +650,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             }
             float l_mine = 0.0f;
             if (tile == 0 && warp == 0) {
-                for (uint32_t t = lane; t < n_tiles; t += 32) l_mine += __ldcg(a.loss_partials + t);
+                for (uint32_t t = lane; t < n_data; t += 32) l_mine += __ldcg(a.loss_partials + t);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) l_mine += __shfl_xor_sync(0xffffffffu, l_mine, o);
                 if (lane == 0)
@@ -651,10 +658,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                         if (r != me) asm volatile("st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(reinterpret_cast<float2*>(row(r, me)) + NMLP), "f"(l_mine), "f"(tag) : "memory");
             }
             if constexpr (ENC == 1) {
-                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
-                    const float g = __ldcg(a.grid_grad + j);
-                    a.grid_grad[j] = 0.0f;
-                    for (uint32_t r = 0; r < R; ++r) row(r, me)[2 * LLS + j] = g;
+                for (uint32_t j = glo + 4 * tid; j < ghi; j += 4 * kTrainThreads) {   // glo, ghi multiples of 4
+                    const float4 g = __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j));
+                    *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    for (uint32_t r = 0; r < R; ++r) *reinterpret_cast<float4*>(row(r, me) + 2 * LLS + j) = g;
                 }
                 __threadfence_system();
                 __syncthreads();
@@ -694,12 +701,14 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     } while ((int32_t)(seen - a.dp_step) < 0);
                 }
                 __syncthreads();
-                for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) {
-                    float g = 0.0f;
-                    for (uint32_t r = 0; r < R; ++r) g += __ldcv(row(me, r) + 2 * LLS + j);
-                    a.grad_f32[NMLP + j] = g;
-                    adam_ema_param(a, NMLP + j, g, E);
-                }
+                grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) {   // rank order: identical sums on every rank
+                    float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    for (uint32_t r = 0; r < R; ++r) {
+                        const float4 v = __ldcv(reinterpret_cast<const float4*>(row(me, r) + 2 * LLS + j));
+                        g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
+                    }
+                    return g;
+                }, false);
             }
         }
     }
@@ -759,7 +768,7 @@ static cudaError_t launch_train_t(const TrainArgs& a, const GridMeta& gm, cudaSt
     const bool multi = a.apply && a.dp_world <= 1 && a.n_steps > 1;
     const void* fn = multi ? reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, true>)
                            : reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, false>);
-    return cudaLaunchCooperativeKernel(fn, dim3(a.n_local / kTT), dim3(kTrainThreads), args, L::kTotal, stream);
+    return cudaLaunchCooperativeKernel(fn, dim3(train_grid(a.n_local)), dim3(kTrainThreads), args, L::kTotal, stream);
 }
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
     return encoding == 0 ? launch_train_t<0>(a, gm, stream) : launch_train_t<1>(a, gm, stream);
