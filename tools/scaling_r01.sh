@@ -7,7 +7,7 @@ run                      > gpurun_out/scaling/dp${N}_fused.json        2> gpurun
 run --shard-frame 8424000 > gpurun_out/scaling/strong4k_${N}.json       2> gpurun_out/scaling/strong4k_${N}.err
 if [ "$N" = "8" ]; then
 run --encoding hash      > gpurun_out/scaling/dp${N}_hash.json         2> gpurun_out/scaling/dp${N}_hash.err
-run --dp nccl            > gpurun_out/scaling/dp${N}_nccl.json         2> gpurun_out/scaling/dp${N}_nccl.err
+true
 fi
 for f in gpurun_out/scaling/*_${N}*.json gpurun_out/scaling/dp${N}_*.json; do python - "$f" <<'PY'
 import json, sys
