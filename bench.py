@@ -96,14 +96,13 @@ class ClockSampler(threading.Thread):
     BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
             0x80: "hw_power_brake"}
 
-    def __init__(self, index, period=0.005):
+    def __init__(self, index, period=0.002):
         super().__init__(daemon=True)
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz, self.err = [], set(), None, None
         self._stop_evt = threading.Event()
-
-    def run(self):
-        try:
+        self._nvml, self._h = None, None
+        try:   # NVML is brought up HERE (main thread, before the timed region): nvmlInit alone outlasts a 60 ms region
             import pynvml
             pynvml.nvmlInit()
             # NVML enumerates physical devices; honour CUDA_VISIBLE_DEVICES when it is a plain index list
@@ -114,17 +113,29 @@ class ClockSampler(threading.Thread):
                     idx = int(vis.split(",")[self.index])
                 except ValueError:
                     pass
-            h = pynvml.nvmlDeviceGetHandleByIndex(idx)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
-            while not self._stop_evt.is_set():
-                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
-                r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in self.BITS.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                time.sleep(self.period)
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self._nvml = pynvml
         except Exception as e:  # NVML missing: report it, never fake a clock
             self.err = repr(e)
+
+    def sample_now(self):
+        """One sample from the calling thread (the bench calls it while the timed launches are still executing)."""
+        if self._nvml is None:
+            return
+        try:
+            self.samples.append(self._nvml.nvmlDeviceGetClockInfo(self._h, self._nvml.NVML_CLOCK_SM))
+            r = self._nvml.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+            for bit, name in self.BITS.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception as e:
+            self.err = repr(e)
+
+    def run(self):
+        while self._nvml is not None and not self._stop_evt.is_set():
+            self.sample_now()
+            time.sleep(self.period)
 
     def stop(self):
         self._stop_evt.set()
@@ -300,6 +311,7 @@ def run_ours(args, enc):
     for i in range(args.steps):
         update(i)
     e1.record(stream)
+    sampler.sample_now()                     # the launches above are still executing: at least one sample under load
     barrier()
     clocks = sampler.stop()
     launches = net.launch_count() - launches0

@@ -16,6 +16,9 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libnrc_b200.so")
+# A/B measurements only (tools/ab_variants.py): another BUILD of the same CUDA library, e.g. build/variants/libnrc_b200_v0.so
+if os.environ.get("NRC_B200_LIB"):
+    LIB_PATH = os.path.abspath(os.environ["NRC_B200_LIB"])
 
 FREQUENCY, HASH = 0, 1            # nrc::InputEncoding (neural_radiance_caching.h:24-27)
 NUM_BATCHES = 4                   # neural_radiance_caching.h:29

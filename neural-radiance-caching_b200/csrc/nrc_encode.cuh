@@ -24,6 +24,40 @@ struct GridMeta {
     uint32_t dense_mask;   // bit l set: level l is NOT hashed (res^3 <= table size, or the stride wrapped to 0)
 };
 
+// NRC_ENC_VARIANT selects how the Frequency / one-blob arithmetic is issued (same mathematics):
+//   0  scalar fp32, FRND for floor / rint (the first version of this round)
+//   1  tri-wave folded to 1 - 4|v - rint(v)|, rint through the 1.5*2^23 magic add (no XU pipe), scalar
+//   2  = 1 with two features per instruction: Blackwell packed fp32 (FFMA2 / FADD2 / FMUL2, one issue slot for two lanes)
+//   3  = 2 plus the one-blob CDF polynomials two bin edges at a time
+#ifndef NRC_ENC_VARIANT
+#define NRC_ENC_VARIANT 3
+#endif
+
+// Packed fp32 pairs live in one 64-bit register (sm_100+: fma/add/mul .f32x2, each lane IEEE round-to-nearest).
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_make(float lo, float hi) {
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f2_split(f2_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) {
+    f2_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) {
+    f2_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) {
+    f2_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+#define NRC_RINT_MAGIC 12582912.0f   // 1.5 * 2^23: (v + M) - M == rint(v) for |v| < 2^22
+
 // Wrapped quartic-kernel CDF sum  c(d) + c(d-1) + c(d+1)  with  c(t) = clamp(P(4t) + 0.5, 0, 1).
 // c saturates for |t| >= 1/4, so at most one of the three terms is unsaturated: with k = rint(d), r = d - k
 // the sum is  clamp(k+1, 0, 3) + (|k| <= 1 ? c(r) : 0).  r is exact, so the live term matches the
@@ -53,6 +87,61 @@ __device__ __forceinline__ void oneblob4(float x, float (&y)[4]) {
     y[0] = c1 - c0; y[1] = c2 - c1; y[2] = c3 - c2; y[3] = c4 - c3;
 }
 
+// Packed form of blob_cdf3 for two dimensions at once (lanes = dims), bin edge b broadcast: the same IEEE operations as
+// blob_cdf3 lane by lane (b - x as fma(x, -1, b): one rounding; rint through the magic add: exact for |b - x| < 2^22),
+// so the results are bit-identical to the scalar form.  The saturating fma and the clamp have no packed form: scalar.
+__device__ __forceinline__ void blob_cdf3_x2(f2_t x2, float b, float& c_lo, float& c_hi) {
+    const f2_t d = f2_fma(x2, f2_make(-1.0f, -1.0f), f2_make(b, b));
+    const f2_t k = f2_add(f2_add(d, f2_make(NRC_RINT_MAGIC, NRC_RINT_MAGIC)), f2_make(-NRC_RINT_MAGIC, -NRC_RINT_MAGIC));
+    const f2_t r = f2_fma(k, f2_make(-1.0f, -1.0f), d);
+    const f2_t q2 = f2_mul(r, r);
+    const f2_t q4 = f2_mul(q2, q2);
+    const float k1 = 16.0f * -(2.0f / 3.0f), k2 = 256.0f * 0.2f;
+    const f2_t inner = f2_fma(q4, f2_make(k2, k2), f2_fma(q2, f2_make(k1, k1), f2_make(1.0f, 1.0f)));
+    const f2_t a = f2_mul(r, f2_make(3.75f, 3.75f));
+    const f2_t kp = f2_add(k, f2_make(1.0f, 1.0f));
+    float a0, a1, i0, i1, kp0, kp1;
+    f2_split(a, a0, a1); f2_split(inner, i0, i1); f2_split(kp, kp0, kp1);
+    c_lo = fminf(fmaxf(kp0 + __saturatef(fmaf(a0, i0, 0.5f)), 0.0f), 3.0f);
+    c_hi = fminf(fmaxf(kp1 + __saturatef(fmaf(a1, i1, 0.5f)), 0.0f), 3.0f);
+}
+// 4 bins of two dimensions (lanes of x2) -> ya / yb.
+template <bool WRAP_LAST>
+__device__ __forceinline__ void oneblob4_x2(f2_t x2, float (&ya)[4], float (&yb)[4]) {
+    float ca[5], cb[5];
+    blob_cdf3_x2(x2, 0.0f, ca[0], cb[0]);
+    blob_cdf3_x2(x2, 0.25f, ca[1], cb[1]);
+    blob_cdf3_x2(x2, 0.5f, ca[2], cb[2]);
+    blob_cdf3_x2(x2, 0.75f, ca[3], cb[3]);
+    if (WRAP_LAST) { ca[4] = ca[0] + 1.0f; cb[4] = cb[0] + 1.0f; }
+    else blob_cdf3_x2(x2, 1.0f, ca[4], cb[4]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { ya[i] = ca[i + 1] - ca[i]; yb[i] = cb[i + 1] - cb[i]; }
+}
+// One-blob of the six angular / roughness inputs q[3..8] -> 12 packed half2 words (dim-major, 2 words per dim).
+template <bool WRAP_LAST>
+__device__ __forceinline__ void oneblob_six(const float (&q)[15], uint32_t* e) {
+#if NRC_ENC_VARIANT >= 3
+#pragma unroll
+    for (int d = 0; d < 6; d += 2) {
+        float ya[4], yb[4];
+        oneblob4_x2<WRAP_LAST>(f2_make(q[3 + d], q[4 + d]), ya, yb);
+        e[2 * d] = pack_h2(ya[0], ya[1]);
+        e[2 * d + 1] = pack_h2(ya[2], ya[3]);
+        e[2 * d + 2] = pack_h2(yb[0], yb[1]);
+        e[2 * d + 3] = pack_h2(yb[2], yb[3]);
+    }
+#else
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+        float y[4];
+        oneblob4<WRAP_LAST>(q[3 + d], y);
+        e[2 * d] = pack_h2(y[0], y[1]);
+        e[2 * d + 1] = pack_h2(y[2], y[3]);
+    }
+#endif
+}
+
 __device__ __forceinline__ float triwave(float x, int f) {
     // scalbnf(x, f-1) is exact, so one fma reproduces  x*2^(f-1) + 0.25 f  with a single rounding
     const float v = fmaf(x, __int_as_float((126 + f) << 23), 0.25f * (float)f);
@@ -60,22 +149,61 @@ __device__ __forceinline__ float triwave(float x, int f) {
     return fmaf(fabsf(r - 0.5f), 4.0f, -1.0f);
 }
 
-// Frequency config: 15 raw floats -> 80 fp16 features packed as 40 half2 words (lo = even feature).
-__device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t (&e)[40]) {
+// Folded tri-wave: with d = v - rint(v) in [-1/2, 1/2] (exact),  |frac(v) - 1/2| = 1/2 - |d|,  so  y = 1 - 4|d|  with ONE
+// rounding (the reference rounds frac(v) - 1/2 first: a 2^-26 difference that the fp16 rounding of the feature hides in all
+// but ~1e-4 of the cases, where the feature moves by one fp16 ulp).  rint through the magic add: |v| < 2^22, i.e. scene
+// coordinates below 4096 / 0.005 units.  No XU-pipe instruction (floorf is FRND, 8 issue cycles per warp).
+__device__ __forceinline__ float triwave_fold(float x, int f) {
+    const float v = fmaf(x, __int_as_float((126 + f) << 23), 0.25f * (float)f);
+    const float n = (v + NRC_RINT_MAGIC) - NRC_RINT_MAGIC;
+    return fmaf(fabsf(v - n), -4.0f, 1.0f);
+}
+// Tri-wave of the three position coordinates -> 18 packed half2 words (j = d*12 + f).
+__device__ __forceinline__ void triwave_xyz(const float (&q)[15], uint32_t* e) {
     float t[36];
+#if NRC_ENC_VARIANT == 0
 #pragma unroll
     for (int d = 0; d < 3; ++d)
 #pragma unroll
         for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave(q[d], f);
+#elif NRC_ENC_VARIANT == 1
+#pragma unroll
+    for (int d = 0; d < 3; ++d)
+#pragma unroll
+        for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave_fold(q[d], f);
+#else
+    // lanes = (x, y): every constant is a broadcast; z: lanes = frequencies (f, f + 1)
+    const f2_t xy = f2_make(q[0], q[1]), zz = f2_make(q[2], q[2]);
+    const f2_t mp = f2_make(NRC_RINT_MAGIC, NRC_RINT_MAGIC), mn = f2_make(-NRC_RINT_MAGIC, -NRC_RINT_MAGIC), neg1 = f2_make(-1.0f, -1.0f);
+#pragma unroll
+    for (int f = 0; f < 12; ++f) {
+        const float s = __int_as_float((126 + f) << 23), o = 0.25f * (float)f;
+        const f2_t v = f2_fma(xy, f2_make(s, s), f2_make(o, o));
+        const f2_t d = f2_fma(f2_add(f2_add(v, mp), mn), neg1, v);
+        float d0, d1;
+        f2_split(d, d0, d1);
+        t[f] = fmaf(fabsf(d0), -4.0f, 1.0f);
+        t[12 + f] = fmaf(fabsf(d1), -4.0f, 1.0f);
+    }
+#pragma unroll
+    for (int f = 0; f < 12; f += 2) {
+        const f2_t v = f2_fma(zz, f2_make(__int_as_float((126 + f) << 23), __int_as_float((127 + f) << 23)),
+                              f2_make(0.25f * (float)f, 0.25f * (float)(f + 1)));
+        const f2_t d = f2_fma(f2_add(f2_add(v, mp), mn), neg1, v);
+        float d0, d1;
+        f2_split(d, d0, d1);
+        t[24 + f] = fmaf(fabsf(d0), -4.0f, 1.0f);
+        t[25 + f] = fmaf(fabsf(d1), -4.0f, 1.0f);
+    }
+#endif
 #pragma unroll
     for (int i = 0; i < 18; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
-#pragma unroll
-    for (int d = 0; d < 6; ++d) {
-        float y[4];
-        oneblob4<true>(q[3 + d], y);
-        e[18 + 2 * d] = pack_h2(y[0], y[1]);
-        e[19 + 2 * d] = pack_h2(y[2], y[3]);
-    }
+}
+
+// Frequency config: 15 raw floats -> 80 fp16 features packed as 40 half2 words (lo = even feature).
+__device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t (&e)[40]) {
+    triwave_xyz(q, e);
+    oneblob_six<true>(q, e + 18);
     e[30] = pack_h2(q[9], q[10]);
     e[31] = pack_h2(q[11], q[12]);
     e[32] = pack_h2(q[13], q[14]);
@@ -147,13 +275,7 @@ __device__ __forceinline__ void grid_levels(const float (&q)[15], const __half2*
 __device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2* __restrict__ grid,
                                             const GridMeta& gm, uint32_t (&e)[32]) {
     grid_levels<true, 0, 16>(q, grid, gm, e);
-#pragma unroll
-    for (int d = 0; d < 6; ++d) {
-        float y[4];
-        oneblob4<false>(q[3 + d], y);
-        e[16 + 2 * d] = pack_h2(y[0], y[1]);
-        e[17 + 2 * d] = pack_h2(y[2], y[3]);
-    }
+    oneblob_six<false>(q, e + 16);
     e[28] = pack_h2(q[9], q[10]);
     e[29] = pack_h2(q[11], q[12]);
     e[30] = pack_h2(q[13], q[14]);
@@ -166,13 +288,7 @@ __device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2*
 template <int HF>
 __device__ __forceinline__ void encode_frequency_half(const float (&q)[15], uint32_t (&e)[20]) {
     if constexpr (HF == 0) {
-        float t[36];
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
-#pragma unroll
-            for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave(q[d], f);
-#pragma unroll
-        for (int i = 0; i < 18; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+        triwave_xyz(q, e);   // same instruction sequence as the query kernel: training and queries see identical features
         float y[4];
         oneblob4<true>(q[3], y);
         e[18] = pack_h2(y[0], y[1]);
