@@ -220,16 +220,15 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         //      accumulate_render_radiance (nrc_helpers.cu:77-129) for the pixel queries -- the radiance is still in registers,
         //      so the separate pass (re-read 12 B radiance, 12 B throughput, 16 B output per pixel) disappears.
         //      `staged`: this tile's throughput / output rows in shared memory, or nullptr (read them from global memory).
-        auto finish_tile = [&](uint32_t t, const uint8_t* staged) {
-            float y[3];
-            {
-                uint32_t v[4];
-                tmem_ld4(tD, v);
-                tmem_wait_ld();
+        auto drain_output = [&](float (&y)[3]) {
+            uint32_t v[4];
+            tmem_ld4(tD, v);
+            tmem_wait_ld();
 #pragma unroll
-                for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
-            }
+            for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
             // D is drained: the next tile's first run_layer orders this read before the MMA that overwrites it.
+        };
+        auto emit_tile = [&](uint32_t t, const uint8_t* staged, const float (&y)[3]) {
             const uint32_t rows = min((uint32_t)kTile, n - t * kTile);
             if (acc.out != nullptr) {
                 const uint32_t px = t * kTile + row;
@@ -264,6 +263,11 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             } else if (row < rows) {
                 dst[row * 3 + 0] = y[0]; dst[row * 3 + 1] = y[1]; dst[row * 3 + 2] = y[2];
             }
+        };
+        auto finish_tile = [&](uint32_t t, const uint8_t* staged) {
+            float y[3];
+            drain_output(y);
+            emit_tile(t, staged, y);
         };
 
         uint32_t t = blockIdx.x * kGroups + g;
