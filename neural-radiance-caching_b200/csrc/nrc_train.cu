@@ -92,11 +92,50 @@ __device__ __forceinline__ void mma_wgrad(uint32_t d, uint32_t delta_img, uint32
         umma_ss(d, umma_desc(delta_img + k * 256, 128, 2048), umma_desc(act_img + k * 256, 128, 2048), idesc, k > 0);
 }
 
+// The optimizer state of ONE matrix parameter, loaded before the grid barrier (it does not depend on the gradient), and
+// the bias-corrected learning rate of its next step count (two powf) evaluated while the barrier is pending.
+struct ParamState {
+    float master, m1, m2, lr;
+    uint32_t steps;
+    __half param, ema;
+};
+__device__ __forceinline__ ParamState load_param_state(const TrainArgs& a, uint32_t i) {
+    ParamState p;
+    p.master = a.master[i]; p.m1 = a.m1[i]; p.m2 = a.m2[i]; p.steps = a.steps[i]; p.param = a.params[i]; p.ema = a.ema[i];
+    const uint32_t cur = p.steps + 1;
+    p.lr = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+    return p;
+}
+// adam_step + ema_step_half_precision for a MATRIX parameter (i < n_mlp) on prefetched state.  Every product / sum is
+// written with explicit round-to-nearest intrinsics so that this path and adam_ema_param (data-parallel path, stand-alone
+// optimizer kernel) round identically whatever the compiler would contract: the replicas of a data-parallel job and a
+// single-GPU run stay bit-identical.
+__device__ __forceinline__ void adam_ema_matrix_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E, uint32_t s, const ParamState& p) {
+    const __half gh = __float2half_rn(g32);
+    a.grads[i] = gh;
+    const float gradient = fmaf(a.l2_reg, p.master, __half2float(gh) / a.loss_scale);
+    const float m1 = fmaf(a.beta1, p.m1, __fmul_rn(1.0f - a.beta1, gradient));
+    const float m2 = fmaf(a.beta2, p.m2, __fmul_rn(1.0f - a.beta2, __fmul_rn(gradient, gradient)));
+    a.m1[i] = m1;
+    a.m2[i] = m2;
+    a.steps[i] = p.steps + 1;
+    const float eff = fminf(fmaxf(p.lr / (sqrtf(m2) + a.eps), 0.0f), 3.402823466e+38f);
+    const float new_weight = fmaf(-eff, m1, p.master);
+    a.master[i] = new_weight;
+    const __half w_half = __float2half_rn(new_weight);
+    a.params[i] = w_half;
+    a.params_img[img_index(i, E)] = w_half;
+    const float old_part = __fmul_rn(__fmul_rn(__half2float(p.ema), a.ema_decay), a.ema_debias_old[s]);
+    const float filtered = __fmul_rn(fmaf(__half2float(w_half), 1.0f - a.ema_decay, old_part), a.ema_debias_new[s]);
+    a.ema[i] = __float2half_rn(filtered);
+}
+
 // ---------------------------------------------------------------- optimizer (per parameter)
 // adam_step (tcnn/optimizers/adam.h:75-118) followed by ema_step_half_precision (ema.h:62-76).  `g32` is the
 // reduced fp32 gradient (loss-scaled); the reference's gradient buffer is fp16 (trainer.h:322-336), so it is
 // rounded to fp16 first.  Also maintains the UMMA image of the fp16 training weights.
 __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E, uint32_t s = 0) {
+    if (i < a.n_mlp) { adam_ema_matrix_param(a, i, g32, E, s, load_param_state(a, i)); return; }
     const __half gh = __float2half_rn(g32);
     a.grads[i] = gh;
     float gradient = __half2float(gh) / a.loss_scale;
@@ -252,16 +291,31 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
 
   for (s = 0; s < n_steps; ++s) {
     const uint32_t first = s * a.n_local + tile * kTT;   // first sample of this tile in this step
-    if (tid == 0 && has_tile) {
-        // s > 0: the weight image was rewritten with generic stores by every CTA in the previous step; the grid barrier
-        // ordered them, this makes them visible to the bulk copy (async proxy).
-        if (s > 0) asm volatile("fence.proxy.async;" ::: "memory");
+    // Frequency, s > 0: the CTA has only ARRIVED at the previous step's second grid barrier; the raw queries and their
+    // encoding do not depend on the other CTAs, so they run while that barrier is pending, and the issuer warp completes
+    // the wait before it fetches the new weight image.  (Hash: the encoding reads grid entries other CTAs updated: it waits
+    // at the end of the step.)
+    constexpr bool kOverlapBarrier = MULTI && ENC == 0;
+    if (tid == 0 && has_tile && in_aligned) {
+        mbar_arrive_expect_tx(in_full, 7680);
+        bulk_g2s(smem + L::kIn, a.in + (size_t)first * 15, 7680, in_full);
+    }
+    if (tid == kWorkerWarps * 32 && has_tile) {
+        if (s > 0) {
+            if (kOverlapBarrier) {
+                uint32_t seen, spins = 0;
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
+                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+                } while ((int32_t)(seen - (a.barrier_target + (2 * (s - 1) + 1) * n_tiles)) < 0);
+                __threadfence();
+            }
+            // the weight image was rewritten with generic stores by every CTA in the previous step; the grid barrier
+            // ordered them, this makes them visible to the bulk copy (async proxy).
+            asm volatile("fence.proxy.async;" ::: "memory");
+        }
         mbar_arrive_expect_tx(w_full, L::kWbytes);
         bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
-        if (in_aligned) {
-            mbar_arrive_expect_tx(in_full, 7680);
-            bulk_g2s(smem + L::kIn, a.in + (size_t)first * 15, 7680, in_full);
-        }
     }
 
     if (!has_tile) {
@@ -401,6 +455,40 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             if (lane == 0) warp_loss[qd] = loss;
         }
         signal();
+        // Per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.  The TMEM loads are
+        // warp-wide (.sync.aligned): every lane executes them, lanes 0..15 store.  Column chunks of 16 are split between the
+        // two halves.  An accumulator is dumped as soon as a commit covers its MMAs -- inside the backward chain, in the
+        // shadow of the next layer's MMAs; only dW_h1 and dW_in are left for the end of the tile.
+        const bool owner = lane < 16;
+        const uint32_t o = qd * 16 + (lane & 15);
+        float* P = a.partials + (size_t)tile * NMLP;
+        auto dump16 = [&](uint32_t col, float* dst) {   // 16 consecutive floats of row o
+            uint32_t v[16];
+            tmem_ld16(tq + col, v);
+            tmem_wait_ld();
+            if (owner) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    reinterpret_cast<float4*>(dst)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                                    __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+            }
+        };
+        auto dump_hidden = [&](int l) {                 // dW_h(l+1), l = 0..3
+#pragma unroll
+            for (int c = 0; c < 2; ++c)
+                dump16(wg_hid_col(E, l) + (hf * 2 + c) * 16, P + 64 * E + l * 4096 + o * 64 + (hf * 2 + c) * 16);
+        };
+        auto dump_out = [&]() {                         // dW_out^T [64 x 16]: element (k = o, c) -> dW_out[c][k]
+            if (hf == 1) {
+                uint32_t v[16];
+                tmem_ld16(tq + wg_out_col(E), v);
+                tmem_wait_ld();
+                if (owner) {
+#pragma unroll
+                    for (int c = 0; c < 16; ++c) P[64 * E + 4 * 4096 + c * 64 + o] = __uint_as_float(v[c]);
+                }
+            }
+        };
         // backward chain: delta_l = (W^T delta_(l+1)) .* [h_l > 0], rounded to fp16
 #pragma unroll
         for (int l = 4; l >= 0; --l) {
@@ -418,8 +506,11 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             for (int c = 0; c < 4; ++c)
                 *reinterpret_cast<uint4*>(row_chunk(dbuf, row, hf * 4 + c)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
             signal();
+            // the commit just waited for covers the weight-gradient MMAs issued before it: dW_out (l = 3), dW_h(l+2) (l <= 2)
+            if (l == 3) dump_out();
+            else if (l <= 2) dump_hidden(l + 1);
         }
-        // all MMAs done: weight-gradient accumulators (and, Hash, dL/d(grid features)) are in TMEM
+        // all MMAs done: the remaining weight-gradient accumulators (and, Hash, dL/d(grid features)) are in TMEM
         wait_mma();
         stamp(3);
         if (warp == 0 && lane == 0) a.loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
@@ -522,41 +613,11 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             level(std::integral_constant<int, 14>{}); level(std::integral_constant<int, 15>{});
         }
         if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
-        // per-tile weight-gradient partials: M = 64 accumulators keep row o in lane (o/16)*32 + o%16.
-        // The TMEM loads are warp-wide (.sync.aligned): every lane executes them, lanes 0..15 store.
-        // Column chunks of 16 are split between the two halves.
-        {
-            const bool owner = lane < 16;
-            const uint32_t o = qd * 16 + (lane & 15);
-            float* P = a.partials + (size_t)tile * NMLP;
-            auto dump16 = [&](uint32_t col, float* dst) {   // 16 consecutive floats of row o
-                uint32_t v[16];
-                tmem_ld16(tq + col, v);
-                tmem_wait_ld();
-                if (owner) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        reinterpret_cast<float4*>(dst)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
-                                                                        __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
-                }
-            };
+        {   // the last two accumulators: dW_in and dW_h1
             constexpr int kInChunks = E / 16;                 // 5 (Frequency) / 4 (Hash)
             constexpr int kSplit = (kInChunks + 1) / 2;       // half 0: chunks [0, kSplit); half 1: the rest
             for (int c = (hf == 0 ? 0 : kSplit); c < (hf == 0 ? kSplit : kInChunks); ++c) dump16(kWgIn + c * 16, P + o * E + c * 16);
-#pragma unroll
-            for (int l = 0; l < 4; ++l)
-#pragma unroll
-                for (int c = 0; c < 2; ++c)
-                    dump16(wg_hid_col(E, l) + (hf * 2 + c) * 16, P + 64 * E + l * 4096 + o * 64 + (hf * 2 + c) * 16);
-            if (hf == 1) {   // dW_out^T [64 x 16]: element (k = o, c) -> dW_out[c][k]
-                uint32_t v[16];
-                tmem_ld16(tq + wg_out_col(E), v);
-                tmem_wait_ld();
-                if (owner) {
-#pragma unroll
-                    for (int c = 0; c < 16; ++c) P[64 * E + 4 * 4096 + c * 64 + o] = __uint_as_float(v[c]);
-                }
-            }
+            dump_hidden(0);
         }
     }
     // ---- phase 2: publish this tile's partials, wait for every tile of the batch
@@ -564,8 +625,15 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     __threadfence();
     tc_fence_before();
     __syncthreads();
+    if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
+    // slice `tile` of the parameters belongs to this CTA in phase 3: at most one matrix parameter per thread.  Its optimizer
+    // state is loaded here, while the barrier is pending (single GPU; the data-parallel branches load it themselves).
+    const uint32_t S = ((NMLP + n_tiles - 1) / n_tiles + 3) & ~3u;     // parameters per CTA (multiple of 4)
+    const uint32_t lo = min((uint32_t)NMLP, tile * S), hi = min((uint32_t)NMLP, lo + S);
+    const bool pre_ok = a.apply && a.dp_world <= 1 && hi - lo <= (uint32_t)kTrainThreads;
+    ParamState pst = {};
+    if (pre_ok && (uint32_t)tid < hi - lo) pst = load_param_state(a, lo + tid);
     if (tid == 0) {
-        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
         uint32_t seen, spins = 0;
         do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
@@ -578,8 +646,6 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
 
     // ---- phase 3: slice c of the gradient: fixed-order sum over tiles, then Adam + EMA (or store for all-reduce)
     {
-        const uint32_t S = ((NMLP + n_tiles - 1) / n_tiles + 3) & ~3u;     // parameters per CTA (multiple of 4)
-        const uint32_t lo = min((uint32_t)NMLP, tile * S), hi = min((uint32_t)NMLP, lo + S);
         const uint32_t ncol4 = (hi - lo) >> 2;                             // NMLP % 4 == 0 -> whole float4 columns
         float4* scratch = reinterpret_cast<float4*>(smem + L::kScratch);   // [groups][ncol4]
         const uint32_t groups = ncol4 == 0 ? 0 : (ncol4 >= (uint32_t)kTrainThreads ? 1 : min((uint32_t)kTrainThreads / ncol4, n_data));
@@ -587,17 +653,18 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             const uint32_t g = w / ncol4, c4 = w - g * ncol4;
             const float* src = a.partials + lo + 4 * c4;
             float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            // batches of 8 independent L2 loads in flight (a dependent chain of ~0.4 us L2 hits otherwise), summed in
-            // increasing tile order
-            for (uint32_t t0 = g; t0 < n_data; t0 += 8 * groups) {
-                float4 v[8];
+            // up to 24 independent L2 loads in flight: the 22 tiles a thread sums for the 16384-sample batch cost ONE L2 round
+            // trip (a dependent chain of ~0.4 us hits otherwise), summed in increasing tile order
+            constexpr int kInFlight = 24;
+            for (uint32_t t0 = g; t0 < n_data; t0 += kInFlight * groups) {
+                float4 v[kInFlight];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) {
+                for (int u = 0; u < kInFlight; ++u) {
                     const uint32_t t = t0 + u * groups;
                     v[u] = t < n_data ? __ldcg(reinterpret_cast<const float4*>(src + (size_t)t * NMLP)) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 }
 #pragma unroll
-                for (int u = 0; u < 8; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+                for (int u = 0; u < kInFlight; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
             }
             scratch[w] = acc;
         }
@@ -617,7 +684,8 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             for (uint32_t j = tid; j < hi - lo; j += kTrainThreads) {
                 const float g = slice_grad(j);
                 a.grad_f32[lo + j] = g;
-                if (a.apply) adam_ema_param(a, lo + j, g, E, s);
+                if (pre_ok) adam_ema_matrix_param(a, lo + j, g, E, s, pst);
+                else if (a.apply) adam_ema_param(a, lo + j, g, E, s);
             }
             if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
                 if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) { return __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j)); }, true);
@@ -721,12 +789,14 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         __syncthreads();
         if (tid == 0) {
             asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
-            uint32_t seen, spins = 0;
-            do {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
-                if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-            } while ((int32_t)(seen - (a.barrier_target + (2 * s + 1) * n_tiles)) < 0);
-            __threadfence();
+            if (!(kOverlapBarrier && has_tile)) {   // otherwise the issuer warp completes the wait after the next encode has started
+                uint32_t seen, spins = 0;
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
+                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+                } while ((int32_t)(seen - (a.barrier_target + (2 * s + 1) * n_tiles)) < 0);
+                __threadfence();
+            }
         }
         __syncthreads();
     }
