@@ -408,20 +408,17 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         }
         signal();
         stamp(1);
-        // forward: h_(l+1) = relu(acc) -> fp16 -> smem; keep the relu mask of this thread's 32 columns in a register
-        uint32_t mask[5];
+        // forward: h_(l+1) = relu(acc) -> fp16 -> smem (the backward pass takes the ReLU mask from these fp16 activations,
+        // like the reference: fully_fused_mlp.cu:150-259 reads the stored forward activations)
 #pragma unroll
         for (int l = 0; l < 5; ++l) {
             wait_mma();
             uint32_t v[32];
             tmem_ld32(tq + kAcc + cb, v);
             tmem_wait_ld();
-            uint32_t m = 0, w[16];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > 0.0f ? 1u : 0u) << i;
+            uint32_t w[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-            mask[l] = m;
 #pragma unroll
             for (int c = 0; c < 4; ++c)
                 *reinterpret_cast<uint4*>(row_chunk(smem + L::kH + l * 16384, row, hf * 4 + c)) =
@@ -462,10 +459,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         const bool owner = lane < 16;
         const uint32_t o = qd * 16 + (lane & 15);
         float* P = a.partials + (size_t)tile * NMLP;
-        auto dump16 = [&](uint32_t col, float* dst) {   // 16 consecutive floats of row o
-            uint32_t v[16];
-            tmem_ld16(tq + col, v);
-            tmem_wait_ld();
+        auto store16 = [&](const uint32_t (&v)[16], float* dst) {   // 16 consecutive floats of row o
             if (owner) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
@@ -473,10 +467,14 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                                                                     __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
             }
         };
-        auto dump_hidden = [&](int l) {                 // dW_h(l+1), l = 0..3
-#pragma unroll
-            for (int c = 0; c < 2; ++c)
-                dump16(wg_hid_col(E, l) + (hf * 2 + c) * 16, P + 64 * E + l * 4096 + o * 64 + (hf * 2 + c) * 16);
+        auto dump_hidden = [&](int l) {                 // dW_h(l+1), l = 0..3: this thread's 32 columns, both loads in flight
+            uint32_t v0[16], v1[16];
+            tmem_ld16(tq + wg_hid_col(E, l) + hf * 32, v0);
+            tmem_ld16(tq + wg_hid_col(E, l) + hf * 32 + 16, v1);
+            tmem_wait_ld();
+            float* dst = P + 64 * E + l * 4096 + o * 64 + hf * 32;
+            store16(v0, dst);
+            store16(v1, dst + 16);
         };
         auto dump_out = [&]() {                         // dW_out^T [64 x 16]: element (k = o, c) -> dW_out[c][k]
             if (hf == 1) {
@@ -496,12 +494,16 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             uint8_t* dbuf = smem + L::kDelta + ((4 - l) & 1) * 16384;
             uint32_t v[32], w[16];
             tmem_ld32(tq + kAcc + cb, v);
+            uint4 hh[4];                       // h_(l+1), this thread's 32 columns (its own stores of the forward pass)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) hh[c] = *reinterpret_cast<const uint4*>(row_chunk(smem + L::kH + l * 16384, row, hf * 4 + c));
             tmem_wait_ld();
-            const uint32_t m = mask[l];
+            const uint32_t* hw = reinterpret_cast<const uint32_t*>(hh);
+            const __half2 zero2 = __float2half2_rn(0.0f);
 #pragma unroll
             for (int i = 0; i < 16; ++i)
-                w[i] = pack_h2((m >> (2 * i)) & 1 ? __uint_as_float(v[2 * i]) : 0.0f,
-                               (m >> (2 * i + 1)) & 1 ? __uint_as_float(v[2 * i + 1]) : 0.0f);
+                w[i] = pack_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])) &
+                       __hgt2_mask(*reinterpret_cast<const __half2*>(&hw[i]), zero2);
 #pragma unroll
             for (int c = 0; c < 4; ++c)
                 *reinterpret_cast<uint4*>(row_chunk(dbuf, row, hf * 4 + c)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
@@ -613,11 +615,22 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             level(std::integral_constant<int, 14>{}); level(std::integral_constant<int, 15>{});
         }
         if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
-        {   // the last two accumulators: dW_in and dW_h1
+        {   // the last two accumulators: dW_in and dW_h1, all loads in flight before the wait
             constexpr int kInChunks = E / 16;                 // 5 (Frequency) / 4 (Hash)
             constexpr int kSplit = (kInChunks + 1) / 2;       // half 0: chunks [0, kSplit); half 1: the rest
-            for (int c = (hf == 0 ? 0 : kSplit); c < (hf == 0 ? kSplit : kInChunks); ++c) dump16(kWgIn + c * 16, P + o * E + c * 16);
-            dump_hidden(0);
+            const int c0 = hf == 0 ? 0 : kSplit, nc = hf == 0 ? kSplit : kInChunks - kSplit;
+            uint32_t vi[kSplit][16], h0[16], h1[16];
+#pragma unroll
+            for (int c = 0; c < kSplit; ++c)
+                if (c < nc) tmem_ld16(tq + kWgIn + (c0 + c) * 16, vi[c]);
+            tmem_ld16(tq + wg_hid_col(E, 0) + hf * 32, h0);
+            tmem_ld16(tq + wg_hid_col(E, 0) + hf * 32 + 16, h1);
+            tmem_wait_ld();
+#pragma unroll
+            for (int c = 0; c < kSplit; ++c)
+                if (c < nc) store16(vi[c], P + o * E + (c0 + c) * 16);
+            store16(h0, P + 64 * E + o * 64 + hf * 32);
+            store16(h1, P + 64 * E + o * 64 + hf * 32 + 16);
         }
     }
     // ---- phase 2: publish this tile's partials, wait for every tile of the batch
