@@ -113,7 +113,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     uint64_t* acc_full = bars + 2 * kGroups;   // [kGroups] throughput + output rows of the tile landed (pipelined loop)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGroups);
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything derived from it (TMEM
+    // addresses, barrier ids, shared-memory bases of the group) in uniform registers instead of R2UR moves per use
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
     const uint32_t tile_stride = gridDim.x * kGroups;
 

@@ -266,7 +266,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
     float* warp_loss = reinterpret_cast<float*>(bars + 5);   // [4]
 
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // provably warp-uniform
     const uint32_t tile = blockIdx.x;
     const uint32_t n_tiles = gridDim.x;              // CTAs = gradient slices of phase 3 (>= data tiles)
     const uint32_t n_data = a.n_local / kTT;         // 128-sample tiles of this launch: CTAs [0, n_data) run phase 1
