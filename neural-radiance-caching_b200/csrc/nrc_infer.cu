@@ -207,14 +207,17 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         };
         auto nothing = [] {};
         auto hidden_epilogue = [&]() {   // D (fp32) -> relu -> fp16 -> A
+            // 16-column pieces, the next piece's TMEM load in flight while the current one is converted (tcgen05.wait::ld waits
+            // for every outstanding load, so a load is issued right AFTER the wait that completes its predecessor)
+            uint32_t v[2][16], w[8];
+            tmem_ld16(tD, v[0]);
 #pragma unroll
-            for (int hcol = 0; hcol < 2; ++hcol) {
-                uint32_t v[32], w[16];
-                tmem_ld32(tD + hcol * 32, v);
+            for (int pc = 0; pc < 4; ++pc) {
                 tmem_wait_ld();
+                if (pc < 3) tmem_ld16(tD + (pc + 1) * 16, v[(pc + 1) & 1]);
 #pragma unroll
-                for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
-                tmem_st16(tA + hcol * 16, w);
+                for (int i = 0; i < 8; ++i) w[i] = pack_relu_h2(__uint_as_float(v[pc & 1][2 * i]), __uint_as_float(v[pc & 1][2 * i + 1]));
+                tmem_st8(tA + pc * 8, w);
             }
         };
 
@@ -311,8 +314,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             }
             for (; t < n_tiles; t += tile_stride) {
                 const bool has_next = t + tile_stride < n_tiles;
-                if (has_next) read_q();                      // raw queries of the next tile -> registers
-                run_layer(std::integral_constant<int, 0>{}, nothing);   // (group barrier inside: stage and acc rows are free)
+                run_layer(std::integral_constant<int, 0>{}, [&] { if (has_next) read_q(); });   // raw queries of the next tile -> registers
                 if (t + 2 * tile_stride < n_tiles) load_in(t + 2 * tile_stride);
                 const bool st = acc_staged(t);
                 if (st && gtid == 0) {
