@@ -465,7 +465,7 @@ def time_reference_gpu(enc, nq):
 
 # (encoding, queries) -> dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the query kernel, from the
 # `ncu --set full` captures summarised in profiles/r01_infer_{frequency,hash}_ncu.txt (algorithmic: 72 B/query = 269.6 MB)
-TRAFFIC_BYTES = {(0, FRAME_QUERIES): 224757760 + 33050112, (1, FRAME_QUERIES): 226331648 + 34014208}
+TRAFFIC_BYTES = {(0, FRAME_QUERIES): 224733696 + 31894272, (1, FRAME_QUERIES): 226329856 + 33507840}
 
 
 def main():

@@ -11,12 +11,15 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
         "sm__cycles_elapsed.max", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
-        "sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg",
+        "sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg", "sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active",
         "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct",
-        "lts__t_bytes.sum.per_second", "l1tex__t_sector_hit_rate.pct", "l1tex__data_pipe_lsu_wavefronts.sum",
+        "lts__t_bytes.sum.per_second", "lts__t_sectors.sum", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+        "l1tex__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__t_requests_pipe_lsu_mem_global_op_ld.sum",
+        "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld_lookup_hit.sum",
+        "l1tex__t_sector_hit_rate.pct", "l1tex__data_pipe_lsu_wavefronts.sum",
         "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
         "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
@@ -49,8 +52,10 @@ def rep(path):
         name = r[h.index("Kernel Name")] if "Kernel Name" in h else "?"
         print(f"# {path}\n# kernel: {name}")
         for k in KEYS:
-            if k in h:
-                i = h.index(k)
+            # some counters carry a section prefix in the raw page ("TPC.TriageCompute.sm__pipe_tensor_..."): match the tail
+            idx = [i for i, name in enumerate(h) if name == k or name.endswith("." + k)]
+            if idx:
+                i = idx[0]
                 print(f"{k:90s} {r[i]:>18s} {rows[1][i]}")
     src = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(src)))
