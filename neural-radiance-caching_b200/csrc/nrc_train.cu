@@ -640,10 +640,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     __syncthreads();
     if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
     // slice `tile` of the parameters belongs to this CTA in phase 3: at most one matrix parameter per thread.  Its optimizer
-    // state is loaded here, while the barrier is pending (single GPU; the data-parallel branches load it themselves).
+    // state is loaded here, while the barrier is pending (the replicas of a data-parallel job hold identical state).
     const uint32_t S = ((NMLP + n_tiles - 1) / n_tiles + 3) & ~3u;     // parameters per CTA (multiple of 4)
     const uint32_t lo = min((uint32_t)NMLP, tile * S), hi = min((uint32_t)NMLP, lo + S);
-    const bool pre_ok = a.apply && a.dp_world <= 1 && hi - lo <= (uint32_t)kTrainThreads;
+    const bool pre_ok = a.apply && hi - lo <= (uint32_t)kTrainThreads;
     ParamState pst = {};
     if (pre_ok && (uint32_t)tid < hi - lo) pst = load_param_state(a, lo + tid);
     if (tid == 0) {
@@ -765,7 +765,8 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 for (uint32_t r = 0; r < R; ++r)     // rank order: identical sums on every rank
                     g += (r == me && u < 2) ? g_mine[u] : poll(reinterpret_cast<const float2*>(row(me, r)) + lo + j);
                 a.grad_f32[lo + j] = g;
-                adam_ema_param(a, lo + j, g, E);
+                if (pre_ok) adam_ema_matrix_param(a, lo + j, g, E, 0, pst);
+                else adam_ema_param(a, lo + j, g, E);
             }
             if (tile == 0 && tid == 0) {
                 float l = 0.0f;
