@@ -49,10 +49,12 @@ namespace nrc {
     public:
         Network() = default;
 
-        ~Network()                  // NRCNetwork.cu:29-33: the destructor only warns
+        ~Network()                  // NRCNetwork.cu:29-33: the destructor only warns (device memory is NOT freed here)
         {
             if (!m_destroyed)
                 std::cerr << "WARNING: NRC Network must be explicitly destroy() in the context it was created in!\n";
+            else if (m_handle)
+                nrc_b200_release(m_handle);     // host-side tombstone of a destroyed network: no CUDA call involved
         }
 
         Network(const Network&) = delete;
@@ -62,7 +64,7 @@ namespace nrc {
         void init(CUstream stream, nrc::InputEncoding encoding)   // NRCNetwork.h:26-31, NRCNetwork.cu:106-112
         {
             m_stream = stream;
-            if (m_handle) {         // init on a live object = full re-create (Device.cpp:2415-2421)
+            if (m_handle) {         // init on a live or destroyed object = full re-create (Device.cpp:2415-2421)
                 check(nrc_b200_reset(m_handle, static_cast<int>(encoding)));
                 check(nrc_b200_set_stream(m_handle, stream));
             } else {
@@ -75,7 +77,8 @@ namespace nrc {
 
         void destroy()              // NRCNetwork.cu:35-39
         {
-            if (m_handle) { nrc_b200_destroy(m_handle); m_handle = nullptr; }
+            // the C handle stays behind as a tombstone: calls after destroy() are no-ops inside the library as well
+            if (m_handle) nrc_b200_destroy(m_handle);
             m_destroyed = true;
         }
 

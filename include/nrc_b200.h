@@ -33,7 +33,7 @@ typedef enum nrc_b200_status {
     NRC_B200_OK = 0,
     NRC_B200_ERR_INVALID = -1,   /* bad argument (reference: std::invalid_argument, NRCNetworkConfigs.h:129-131) */
     NRC_B200_ERR_CUDA = -2,      /* CUDA runtime failure (reference: std::runtime_error from CUDA_CHECK_THROW) */
-    NRC_B200_ERR_DESTROYED = -3  /* informational: call on a destroyed handle is a no-op (NRCNetwork.cu:43,66) */
+    NRC_B200_ERR_DESTROYED = -3  /* informational: call on a destroyed (not yet released) handle is a no-op (NRCNetwork.cu:43,66) */
 } nrc_b200_status;
 
 typedef struct nrc_b200_network* nrc_b200_handle;
@@ -44,8 +44,12 @@ typedef struct nrc_b200_network* nrc_b200_handle;
  * xavier-uniform initialisation (the reference uses 1337, trainer.h:50-57). */
 int nrc_b200_create(int encoding, void* cu_stream, nrc_b200_handle* out);
 int nrc_b200_create_ex(int encoding, int log2_hashmap_size, uint64_t seed, void* cu_stream, nrc_b200_handle* out);
-/* Network::destroy()  NRCNetwork.cu:35-39 */
+/* Network::destroy()  NRCNetwork.cu:35-39.  Frees every device / pinned allocation.  The handle itself stays valid as a
+ * tombstone: later calls on it return NRC_B200_ERR_DESTROYED without doing anything (the reference's silent no-ops,
+ * NRCNetwork.cu:43,66), nrc_b200_reset revives it (Network::init after destroy), nrc_b200_release frees it. */
 int nrc_b200_destroy(nrc_b200_handle h);
+/* Frees the handle (destroying the network first if it is still alive); the pointer is dead afterwards. */
+int nrc_b200_release(nrc_b200_handle h);
 /* Network::init on a live object = full reset (new weights, optimizer state zeroed)  Device.cpp:2415-2421 */
 int nrc_b200_reset(nrc_b200_handle h, int encoding);
 
@@ -64,6 +68,13 @@ int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr);
 int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr);
 
 /* ---- additions without a reference counterpart ------------------------------------------------------ */
+/* Accumulator precision of the QUERY kernel's six matrix products.  NRC_B200_ACC_FP32 (default): fp32 accumulators in tensor
+ * memory, every layer output rounded to fp16 where the reference stores fp16.  NRC_B200_ACC_FP16: fp16 accumulators, rounded
+ * after every 16-wide K block -- the arithmetic of the reference's wmma::accumulator<__half> fragments (tcnn
+ * fully_fused_mlp.cu:68): "reference-exact" queries at the same speed class. */
+#define NRC_B200_ACC_FP32 0
+#define NRC_B200_ACC_FP16 1
+int nrc_b200_set_accumulator(nrc_b200_handle h, int mode);
 /* Host-buffer query: chunked H2D / kernel / D2H pipeline inside the call (synchronous).  Page-locked caller
  * buffers are DMA'd directly; pageable ones are staged through an internal pinned ring. */
 int nrc_b200_infer_host(nrc_b200_handle h, const float* queries_h, float* radiance_h, uint32_t n);
@@ -91,6 +102,12 @@ int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out);
 int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_handles);
 int nrc_b200_train_dp(nrc_b200_handle h, const float* queries_d, const float* targets_d, uint32_t n_local,
                       uint32_t n_global, void* cu_stream, float* loss_h);
+/* The same exchange between `world` handles of ONE process, one per GPU (handles[r] = rank r; peer access instead of CUDA IPC),
+ * driven from one host thread or one thread per handle: every entry point makes its handle's device current for the call.
+ * On a connected handle nrc_b200_train / _train_batches / _train_shuffled / _update train on the GLOBAL batch of
+ * world x 16384 samples (loss and gradient normalised by it) and must be called on every rank; a peer that stays silent for
+ * NRC_B200_DP_TIMEOUT_MS (environment, default 30000) makes the next call on the waiting handle return NRC_B200_ERR_CUDA. */
+int nrc_b200_dp_connect_local(nrc_b200_handle* handles, int world);
 
 /* ---- NEXT rows: the helper kernels either side of the network in Device::render ----------- */
 typedef struct nrc_b200_training_record {       /* nrc::TrainingRecord, neural_radiance_caching.h:57-78 (28 bytes) */
@@ -126,6 +143,9 @@ int nrc_b200_train_batches(nrc_b200_handle h, const float* queries_d, const floa
 uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed);
 int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
                                 int num_records, uint32_t seed, void* cu_stream);
+/* permute_train_data with the caller's permutation (e.g. the reference's cuRAND + CUB result): dst[d] = src[permutation[d] % n]. */
+int nrc_b200_permute_train_data_with(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
+                                     const int* permutation_d, int num_records, void* cu_stream);
 /* Fused: the training step on batch `batch_index` (0..3) of the permuted data without materialising it; identical
  * result to nrc_b200_permute_train_data followed by nrc_b200_train on dst + batch_index*16384. */
 int nrc_b200_train_shuffled(nrc_b200_handle h, const float* q_src_d, const float* t_src_d, int num_records, uint32_t seed,

@@ -37,7 +37,9 @@ ABI_SYMBOLS = [
     "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline", "nrc_b200_dp_export", "nrc_b200_dp_connect", "nrc_b200_train_dp",
     "nrc_b200_accumulate_render_radiance", "nrc_b200_propagate_train_radiance", "nrc_b200_permutation",
     "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_train_batches", "nrc_b200_adjust_tile_size", "nrc_b200_update",
+    "nrc_b200_release", "nrc_b200_set_accumulator", "nrc_b200_dp_connect_local", "nrc_b200_permute_train_data_with",
 ]
+ACC_FP32, ACC_FP16 = 0, 1         # nrc_b200_set_accumulator
 
 
 # nrc::RenderMode (neural_radiance_caching.h:13-22)
@@ -112,6 +114,10 @@ def lib():
         L.nrc_b200_dp_export.argtypes = [vp, vp]
         L.nrc_b200_dp_connect.argtypes = [vp, i32, i32, vp]
         L.nrc_b200_train_dp.argtypes = [vp, vp, vp, u32, u32, vp, P(f32)]
+        L.nrc_b200_release.argtypes = [vp]
+        L.nrc_b200_set_accumulator.argtypes = [vp, i32]
+        L.nrc_b200_dp_connect_local.argtypes = [P(vp), i32]
+        L.nrc_b200_permute_train_data_with.argtypes = [vp, vp, vp, vp, vp, i32, vp]
         _lib = L
     return _lib
 
@@ -130,8 +136,11 @@ def _ptr(x):
 
 
 def _check(rc):
-    if rc == 0 or rc == -3:      # -3: call on a destroyed network, silent no-op (NRCNetwork.cu:43,66)
-        return
+    """True when the call ran; False for a call on a destroyed network (-3: silent no-op, NRCNetwork.cu:43,66)."""
+    if rc == 0:
+        return True
+    if rc == -3:
+        return False
     msg = lib().nrc_b200_last_error().decode()
     if rc == -1:
         raise ValueError(msg)    # std::invalid_argument (NRCNetworkConfigs.h:129-131)
@@ -151,6 +160,17 @@ def propagate_train_radiance(end_vertices_d, end_radiance_d, records_d, targets_
 def permute_train_data(q_src_d, t_src_d, q_dst_d, t_dst_d, num_records, seed, stream=None):
     _check(lib().nrc_b200_permute_train_data(_ptr(q_src_d), _ptr(t_src_d), _ptr(q_dst_d), _ptr(t_dst_d), int(num_records),
                                              int(seed), _ptr(stream)))
+
+
+def permute_train_data_with(q_src_d, t_src_d, q_dst_d, t_dst_d, permutation_d, num_records, stream=None):
+    _check(lib().nrc_b200_permute_train_data_with(_ptr(q_src_d), _ptr(t_src_d), _ptr(q_dst_d), _ptr(t_dst_d), _ptr(permutation_d),
+                                                  int(num_records), _ptr(stream)))
+
+
+def dp_connect_local(networks):
+    """Connects the data-parallel exchange between Network objects of THIS process (one per GPU), rank = list index."""
+    arr = (ctypes.c_void_p * len(networks))(*[n._h for n in networks])
+    _check(lib().nrc_b200_dp_connect_local(arr, len(networks)))
 
 
 def permutation(i, seed):
@@ -177,8 +197,8 @@ class Network:
 
     # template<bool Verbose> void init(CUstream, nrc::InputEncoding)     NRCNetwork.h:26-31
     def init(self, stream, encoding, verbose=False, log2_hashmap_size=15, seed=1337):
-        if self._h is not None:              # init on a live object = full re-create (NRCNetwork.cu:106-112)
-            _check(lib().nrc_b200_destroy(self._h))
+        if self._h is not None:              # init on a live (or destroyed) object = full re-create (NRCNetwork.cu:106-112)
+            _check(lib().nrc_b200_release(self._h))
             self._h = None
         h = ctypes.c_void_p()
         _check(lib().nrc_b200_create_ex(int(encoding), int(log2_hashmap_size), int(seed), _ptr(stream), ctypes.byref(h)))
@@ -187,9 +207,22 @@ class Network:
             print(f"nrc_b200 network: encoding={'Frequency' if encoding == 0 else 'Hash'} n_params={self.n_params()}")
 
     def destroy(self):                       # NRCNetwork.cu:35-39
+        """Frees the device memory; the handle stays behind as a tombstone (later calls are silent no-ops, as in the
+        reference) until the object is re-initialised or garbage-collected."""
         if self._h is not None:
             _check(lib().nrc_b200_destroy(self._h))
-            self._h = None
+
+    def __del__(self):
+        try:
+            if self._h is not None:
+                lib().nrc_b200_release(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def set_accumulator(self, mode):
+        """ACC_FP32 (default) / ACC_FP16 (the reference's fp16-accumulator arithmetic) for the query kernel."""
+        _check(lib().nrc_b200_set_accumulator(self._h, int(mode)))
 
     def train(self, batchInputs_d, batchTargets_d, stream=None, want_loss=False):   # NRCNetwork.cu:41-62
         """One optimizer step on BATCH_SIZE samples.  Returns the loss (host float, forces a stream sync as the
@@ -197,9 +230,9 @@ class Network:
         if self._h is None:
             return None
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train(self._h, _ptr(batchInputs_d), _ptr(batchTargets_d), _ptr(stream),
+        ran = _check(lib().nrc_b200_train(self._h, _ptr(batchInputs_d), _ptr(batchTargets_d), _ptr(stream),
                                     ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        return loss.value if (want_loss and ran) else None
 
     def infer(self, inputs_d, outputs_d, numInputs, stream=None):                   # NRCNetwork.cu:64-83
         if self._h is None:
@@ -224,9 +257,9 @@ class Network:
 
     def train_host(self, inputs_h, targets_h, want_loss=False):
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train_host(self._h, _ptr(inputs_h), _ptr(targets_h),
+        ran = _check(lib().nrc_b200_train_host(self._h, _ptr(inputs_h), _ptr(targets_h),
                                          ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        return loss.value if (want_loss and ran) else None
 
     def train_grad(self, inputs_d, targets_d, n_local, n_global, stream=None):
         """Gradient of this rank's shard; returns the device pointer of the fp32 gradient (n_params floats)."""
@@ -237,8 +270,8 @@ class Network:
 
     def train_apply(self, stream=None, want_loss=False):
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train_apply(self._h, _ptr(stream), ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        ran = _check(lib().nrc_b200_train_apply(self._h, _ptr(stream), ctypes.byref(loss) if want_loss else None))
+        return loss.value if (want_loss and ran) else None
 
     def dp_export(self):
         """64-byte CUDA IPC handle of this rank's exchange buffer (bytes)."""
@@ -253,23 +286,23 @@ class Network:
 
     def train_dp(self, inputs_d, targets_d, n_local, n_global, stream=None, want_loss=False):
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train_dp(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global), _ptr(stream),
+        ran = _check(lib().nrc_b200_train_dp(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global), _ptr(stream),
                                        ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        return loss.value if (want_loss and ran) else None
 
     # ---- NEXT rows: the per-frame sequence around the network (Device::render) ------------------------------
     def train_batches(self, queries_d, targets_d, n_batches, stream=None, want_loss=False):
         """n_batches consecutive train() calls (Device::nrcTrainRadiance) as one launch; returns the mean loss if asked."""
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train_batches(self._h, _ptr(queries_d), _ptr(targets_d), int(n_batches), _ptr(stream),
+        ran = _check(lib().nrc_b200_train_batches(self._h, _ptr(queries_d), _ptr(targets_d), int(n_batches), _ptr(stream),
                                             ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        return loss.value if (want_loss and ran) else None
 
     def train_shuffled(self, q_src_d, t_src_d, num_records, seed, batch_index, stream=None, want_loss=False):
         loss = ctypes.c_float()
-        _check(lib().nrc_b200_train_shuffled(self._h, _ptr(q_src_d), _ptr(t_src_d), int(num_records), int(seed),
+        ran = _check(lib().nrc_b200_train_shuffled(self._h, _ptr(q_src_d), _ptr(t_src_d), int(num_records), int(seed),
                                              int(batch_index), _ptr(stream), ctypes.byref(loss) if want_loss else None))
-        return loss.value if want_loss else None
+        return loss.value if (want_loss and ran) else None
 
     def update(self, frame, stream=None, want_stat=False):
         """frame: nrc_b200.Frame.  Returns TrainingStat when want_stat (one synchronisation), else None."""

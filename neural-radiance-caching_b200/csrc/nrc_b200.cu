@@ -27,6 +27,19 @@ static int fail(int code, const std::string& msg) { g_last_error = msg; return c
             return fail(NRC_B200_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_));      \
     } while (0)
 
+// One handle = one device + one stream (SURVEY.md 8b "Threading"): every entry point makes the handle's device current
+// for the duration of the call and restores the caller's, so several handles on different GPUs can be driven from one
+// thread (or one each from several threads).
+struct DeviceGuard {
+    int prev = -1; bool switched = false;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) == cudaSuccess && prev != dev) switched = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() { if (switched) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 struct nrc_b200_network {
     int encoding = 0, log2_hashmap = 15, device = 0, num_sms = 148;
     uint64_t seed = 1337;
@@ -36,10 +49,12 @@ struct nrc_b200_network {
     // parameter block (device)
     float* master = nullptr; __half* params = nullptr; __half* ema = nullptr; __half* grads = nullptr;
     __half* params_img = nullptr;   // UMMA shared-memory image of the fp16 training MLP weights (bulk-copied by the step kernel)
+    __half* ema_img = nullptr;      // the same image of the fp16 EMA (= inference) MLP weights (bulk-copied by the query kernel)
     uint32_t* barrier_counter = nullptr; uint32_t barrier_total = 0;
     long long* timeline = nullptr;   // debug: per-tile phase stamps of the step kernel
     // data-parallel exchange over NVLink peer memory (nrc_b200_dp_*): one IPC allocation [xbuf | xflag] per rank
     void* dp_local = nullptr; void* dp_peer[kMaxDpRanks] = {}; int dp_rank = 0, dp_world = 1;
+    bool dp_shared_process = false;  // peers are handles of this process (peer access), not CUDA IPC mappings
     uint32_t x_stride = 0; size_t xbuf_bytes = 0;   // grid barrier of the cooperative step kernel
     float* m1 = nullptr; float* m2 = nullptr; uint32_t* steps = nullptr;
     // training scratch (device)
@@ -60,8 +75,27 @@ struct nrc_b200_network {
     float* train_in_d = nullptr; float* train_tgt_d = nullptr;   // staging for train_host (one 16384 batch)
     uint64_t launches = 0;
     bool destroyed = false;
+    int acc16 = 0;                   // 1: query kernel with fp16 accumulators (the reference's wmma accumulator<__half> arithmetic)
+    uint32_t dp_seq = 0;             // data-parallel exchange sequence number (tags / flags / buffer parity); never reset while connected
+    uint32_t* err_host = nullptr;    // pinned, device-mapped word the kernels raise on a peer time-out (instead of a trap)
+    uint32_t* err_dev = nullptr;
+    uint32_t dp_timeout_ms = 30000;  // NRC_B200_DP_TIMEOUT_MS
 };
 typedef nrc_b200_network Net;
+
+static int device_error(Net* h) {
+    const uint32_t code = *(volatile uint32_t*)h->err_host;
+    return fail(NRC_B200_ERR_CUDA, "data-parallel exchange: a peer did not deliver exchange step " + std::to_string(code) +
+                                       " within " + std::to_string(h->dp_timeout_ms) + " ms (NRC_B200_DP_TIMEOUT_MS); the replicas are out of sync");
+}
+// Common prologue of the per-handle entry points: null -> invalid argument; destroyed -> the reference's silent no-op
+// (NRCNetwork.cu:43,66), reported as NRC_B200_ERR_DESTROYED; the handle's device made current for the call; an error
+// a kernel raised earlier (peer time-out) is reported instead of launching more work.
+#define ENTER(h)                                                                   \
+    if (!(h)) return fail(NRC_B200_ERR_INVALID, "null handle");                    \
+    if ((h)->destroyed) return NRC_B200_ERR_DESTROYED;                             \
+    DeviceGuard guard_((h)->device);                                               \
+    if ((h)->err_host && *(volatile uint32_t*)(h)->err_host) return device_error(h)
 
 static constexpr uint32_t kMaxTrainTiles = NRC_B200_BATCH_SIZE / 128;
 
@@ -107,17 +141,17 @@ static float u01(uint64_t& s) { return (float)(splitmix64(s) >> 40) * (1.0f / 16
 
 static void dp_teardown(Net* n) {
     for (int r = 0; r < kMaxDpRanks; ++r) {
-        if (n->dp_peer[r] && r != n->dp_rank) cudaIpcCloseMemHandle(n->dp_peer[r]);
+        if (n->dp_peer[r] && r != n->dp_rank && !n->dp_shared_process) cudaIpcCloseMemHandle(n->dp_peer[r]);
         n->dp_peer[r] = nullptr;
     }
     cudaFree(n->dp_local);
-    n->dp_local = nullptr; n->dp_world = 1; n->dp_rank = 0;
+    n->dp_local = nullptr; n->dp_world = 1; n->dp_rank = 0; n->dp_shared_process = false;
 }
 
 static void free_all(Net* n) {
     cudaFree(n->master); cudaFree(n->params); cudaFree(n->ema); cudaFree(n->grads);
-    cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps); cudaFree(n->params_img); cudaFree(n->barrier_counter);
-    n->params_img = nullptr; n->barrier_counter = nullptr; n->barrier_total = 0;
+    cudaFree(n->m1); cudaFree(n->m2); cudaFree(n->steps); cudaFree(n->params_img); cudaFree(n->ema_img); cudaFree(n->barrier_counter);
+    n->params_img = n->ema_img = nullptr; n->barrier_counter = nullptr; n->barrier_total = 0;
     cudaFree(n->timeline); n->timeline = nullptr;
     dp_teardown(n);
     cudaFree(n->partials); cudaFree(n->grid_grad); cudaFree(n->loss_partials); cudaFree(n->grad_f32); cudaFree(n->loss_d);
@@ -138,6 +172,8 @@ static void free_all(Net* n) {
     n->host_chunk = 0;
     cudaFree(n->train_in_d); cudaFree(n->train_tgt_d);
     n->train_in_d = n->train_tgt_d = nullptr;
+    if (n->err_host) cudaFreeHost(n->err_host);
+    n->err_host = n->err_dev = nullptr;
 }
 
 // Uploads fp32 master weights, derives the fp16 copy (trainer.h:83-86), zeroes EMA (ema.h:93-94) and Adam state.
@@ -155,7 +191,10 @@ static int upload_master(Net* n, const float* host_master) {
     if (n->grid_grad) CU(cudaMemsetAsync(n->grid_grad, 0, (size_t)(n->n_params - n->n_mlp) * 4, n->stream));
     CU(cudaMemsetAsync(n->loss_d, 0, 4, n->stream));
     CU(launch_make_image(n->params, n->params_img, n->enc_width, n->n_mlp, n->stream));
+    CU(cudaMemsetAsync(n->ema_img, 0, (size_t)n->n_mlp * 2, n->stream));
     CU(cudaStreamSynchronize(n->stream));  // host vectors go out of scope
+    // The optimizer step counter restarts; the data-parallel exchange sequence (dp_seq: tags, flags, buffer parity) does
+    // NOT -- stale tags of an earlier run can never match a later step (every rank must re-upload the same weights).
     n->step = 0;
     n->pending_tiles = 0;
     return NRC_B200_OK;
@@ -173,6 +212,7 @@ static int build_model(Net* n) {
     CU(cudaMalloc(&n->grads, P * 2)); CU(cudaMalloc(&n->m1, P * 4)); CU(cudaMalloc(&n->m2, P * 4));
     CU(cudaMalloc(&n->steps, P * 4)); CU(cudaMalloc(&n->grad_f32, P * 4));
     CU(cudaMalloc(&n->params_img, (size_t)n->n_mlp * 2));
+    CU(cudaMalloc(&n->ema_img, (size_t)n->n_mlp * 2));
     CU(cudaMalloc(&n->barrier_counter, 4));
     CU(cudaMemset(n->barrier_counter, 0, 4));
     n->barrier_total = 0;
@@ -181,6 +221,12 @@ static int build_model(Net* n) {
     CU(cudaMalloc(&n->loss_d, 4));
     if (P > n->n_mlp) CU(cudaMalloc(&n->grid_grad, (P - n->n_mlp) * 4));
     CU(cudaMallocHost(&n->loss_pinned, 16));
+    CU(cudaHostAlloc(&n->err_host, 4, cudaHostAllocMapped));
+    *n->err_host = 0;
+    CU(cudaHostGetDevicePointer(&n->err_dev, n->err_host, 0));
+    // cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute: set it for the device of THIS handle
+    CU(configure_infer_kernels());
+    CU(configure_train_kernels());
     CU(cudaMalloc(&n->loss4_d, 16));
     CU(cudaMemset(n->loss4_d, 0, 16));
     std::vector<float> m(P);
@@ -207,8 +253,9 @@ int nrc_b200_create_ex(int encoding, int log2_hashmap_size, uint64_t seed, void*
         return fail(NRC_B200_ERR_INVALID, "log2_hashmap_size must be in [12, 24]");
     Net* n = new Net();
     n->encoding = encoding; n->log2_hashmap = log2_hashmap_size; n->seed = seed; n->stream = (cudaStream_t)cu_stream;
+    if (const char* e = getenv("NRC_B200_DP_TIMEOUT_MS")) { const long v = atol(e); if (v > 0) n->dp_timeout_ms = (uint32_t)v; }
     cudaDeviceProp prop;
-    cudaError_t e = cudaGetDevice(&n->device);
+    cudaError_t e = cudaGetDevice(&n->device);      // the device current at create owns the handle (Device.cpp:2296)
     if (e == cudaSuccess) e = cudaGetDeviceProperties(&prop, n->device);
     if (e != cudaSuccess) { delete n; return fail(NRC_B200_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e)); }
     if (prop.major != 10) {
@@ -225,9 +272,21 @@ int nrc_b200_create_ex(int encoding, int log2_hashmap_size, uint64_t seed, void*
 int nrc_b200_create(int encoding, void* cu_stream, nrc_b200_handle* out) {
     return nrc_b200_create_ex(encoding, 15, 1337, cu_stream, out);
 }
+// Network::destroy (NRCNetwork.cu:35-39): frees every device / pinned allocation.  The (small) host struct stays behind as a
+// tombstone so that later calls on the handle are the reference's silent no-ops (NRC_B200_ERR_DESTROYED) instead of a
+// use-after-free; nrc_b200_reset revives it, nrc_b200_release frees it.
 int nrc_b200_destroy(nrc_b200_handle h) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (!h->destroyed) { cudaStreamSynchronize(h->stream); free_all(h); h->destroyed = true; }
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    DeviceGuard guard_(h->device);
+    cudaStreamSynchronize(h->stream);
+    free_all(h);
+    h->destroyed = true;
+    return NRC_B200_OK;
+}
+int nrc_b200_release(nrc_b200_handle h) {
+    if (!h) return NRC_B200_OK;
+    if (!h->destroyed) nrc_b200_destroy(h);
     delete h;
     return NRC_B200_OK;
 }
@@ -235,24 +294,40 @@ int nrc_b200_reset(nrc_b200_handle h, int encoding) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
     if (encoding != NRC_B200_FREQUENCY && encoding != NRC_B200_HASH)
         return fail(NRC_B200_ERR_INVALID, "Unsupported input encoding");
-    CU(cudaStreamSynchronize(h->stream));
-    free_all(h);
+    DeviceGuard guard_(h->device);
+    if (!h->destroyed) {
+        CU(cudaStreamSynchronize(h->stream));
+        free_all(h);
+    }
     h->encoding = encoding;
-    return build_model(h);
+    h->step = 0; h->dp_seq = 0; h->pending_tiles = 0;
+    int rc = build_model(h);
+    h->destroyed = rc != NRC_B200_OK;
+    if (rc != NRC_B200_OK) free_all(h);
+    return rc;
 }
 int nrc_b200_set_stream(nrc_b200_handle h, void* s) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
     h->stream = (cudaStream_t)s;
     return NRC_B200_OK;
 }
 int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr) {
     if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
     h->lr = lr;
     return NRC_B200_OK;
 }
 int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr) {
     if (!h || !lr) return fail(NRC_B200_ERR_INVALID, "null argument");
-    *lr = h->lr;
+    *lr = h->lr;                     // the hyper-parameter outlives destroy(), like Network::getLearningRate (NRCNetwork.cu:101-104)
+    return NRC_B200_OK;
+}
+int nrc_b200_set_accumulator(nrc_b200_handle h, int mode) {
+    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
+    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (mode != NRC_B200_ACC_FP32 && mode != NRC_B200_ACC_FP16) return fail(NRC_B200_ERR_INVALID, "unknown accumulator mode");
+    h->acc16 = mode == NRC_B200_ACC_FP16;
     return NRC_B200_OK;
 }
 int nrc_b200_launch_count(nrc_b200_handle h, uint64_t* c) {
@@ -282,6 +357,7 @@ static void* param_ptr(Net* n, int kind, size_t* elem) {
 }
 int nrc_b200_get_params(nrc_b200_handle h, int kind, void* dst) {
     if (!h || !dst || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    DeviceGuard guard_(h->device);
     size_t es; void* p = param_ptr(h, kind, &es);
     if (!p) return fail(NRC_B200_ERR_INVALID, "unknown parameter kind");
     CU(cudaStreamSynchronize(h->stream));
@@ -290,29 +366,34 @@ int nrc_b200_get_params(nrc_b200_handle h, int kind, void* dst) {
 }
 int nrc_b200_set_params(nrc_b200_handle h, int kind, const void* src) {
     if (!h || !src || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    DeviceGuard guard_(h->device);
     size_t es; void* p = param_ptr(h, kind, &es);
     if (!p) return fail(NRC_B200_ERR_INVALID, "unknown parameter kind");
     CU(cudaStreamSynchronize(h->stream));
     CU(cudaMemcpy(p, src, es * h->n_params, cudaMemcpyHostToDevice));
-    if (kind == NRC_B200_PARAMS_TRAIN_F16) {
-        CU(launch_make_image(h->params, h->params_img, h->enc_width, h->n_mlp, h->stream));
+    if (kind == NRC_B200_PARAMS_TRAIN_F16 || kind == NRC_B200_PARAMS_EMA_F16) {   // keep the UMMA images current
+        CU(launch_make_image(kind == NRC_B200_PARAMS_TRAIN_F16 ? h->params : h->ema,
+                             kind == NRC_B200_PARAMS_TRAIN_F16 ? h->params_img : h->ema_img, h->enc_width, h->n_mlp, h->stream));
         CU(cudaStreamSynchronize(h->stream));
     }
     return NRC_B200_OK;
 }
 int nrc_b200_load_master(nrc_b200_handle h, const float* m) {
     if (!h || !m || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    DeviceGuard guard_(h->device);
     return upload_master(h, m);
 }
 
 // ---------------------------------------------------------------- inference
+static cudaError_t run_infer(Net* h, const float* q, float* r, uint32_t n, cudaStream_t stream, const AccumArgs* acc = nullptr) {
+    return launch_infer(h->encoding, h->acc16, q, r, n, h->ema, h->ema_img, h->gm, h->num_sms, stream, acc);
+}
 int nrc_b200_infer(nrc_b200_handle h, const float* q, float* r, uint32_t n, void* cu_stream) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;  // silent no-op, NRCNetwork.cu:66
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (n == 0) return NRC_B200_OK;
     if (!q || !r) return fail(NRC_B200_ERR_INVALID, "null device buffer");
-    CU(launch_infer(h->encoding, q, r, n, h->ema, h->gm, h->num_sms, h->stream));
+    CU(run_infer(h, q, r, n, h->stream));
     h->launches += 1;
     return NRC_B200_OK;
 }
@@ -325,8 +406,7 @@ static bool is_pinned_host(const void* p) {
 
 // Host buffers: 3-deep pipeline of (pinned copy-in -> H2D -> kernel -> D2H -> copy-out) over chunks.
 int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (n == 0) return NRC_B200_OK;
     if (!q || !r) return fail(NRC_B200_ERR_INVALID, "null host buffer");
     const uint32_t want = 1u << 18;  // queries per chunk: 15.7 MB in, 3.1 MB out
@@ -359,7 +439,7 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
             const float* src = q + (size_t)c * chunk * 15;
             if (!q_pinned) { memcpy(h->pin_in[s], src, (size_t)cnt * 60); src = h->pin_in[s]; }
             CU(cudaMemcpyAsync(h->dev_in[s], src, (size_t)cnt * 60, cudaMemcpyHostToDevice, h->hstream[s]));
-            CU(launch_infer(h->encoding, h->dev_in[s], h->dev_out[s], cnt, h->ema, h->gm, h->num_sms, h->hstream[s]));
+            CU(run_infer(h, h->dev_in[s], h->dev_out[s], cnt, h->hstream[s]));
             h->launches += 1;
             float* dst = r_pinned ? r + (size_t)c * chunk * 3 : h->pin_out[s];
             CU(cudaMemcpyAsync(dst, h->dev_out[s], (size_t)cnt * 12, cudaMemcpyDeviceToHost, h->hstream[s]));
@@ -370,29 +450,35 @@ int nrc_b200_infer_host(nrc_b200_handle h, const float* q, float* r, uint32_t n)
 }
 
 // ---------------------------------------------------------------- training
-// h->step is the (first) optimizer step this launch applies; n_steps > 1: steps h->step .. h->step + n_steps - 1.
+// `first_step` is the (first) optimizer step this launch applies; n_steps > 1: steps first_step .. first_step + n_steps - 1.
+// Nothing in the handle is advanced here: the callers commit step / barrier / exchange counters only AFTER the launch has
+// been accepted (a failed launch must not leave the host's barrier target ahead of the device counter).
 static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_local, uint32_t n_global, int apply,
                             uint32_t n_steps = 1) {
     TrainArgs a{};
+    const uint32_t first_step = h->step + 1;
     a.in = q; a.targets = t; a.n_local = n_local; a.n_global = n_global;
-    a.master = h->master; a.params = h->params; a.params_img = h->params_img; a.ema = h->ema; a.grads = h->grads;
+    a.master = h->master; a.params = h->params; a.params_img = h->params_img; a.ema = h->ema; a.ema_img = h->ema_img; a.grads = h->grads;
     a.m1 = h->m1; a.m2 = h->m2; a.steps = h->steps;
     a.partials = h->partials; a.grid_grad = h->grid_grad; a.loss_partials = h->loss_partials;
     a.grad_f32 = h->grad_f32; a.loss_out = h->loss_d;
-    a.barrier_counter = h->barrier_counter; a.barrier_target = h->barrier_total;
+    a.barrier_counter = h->barrier_counter;
+    a.barrier_target = h->barrier_total + train_grid(n_local);   // value of the counter once every CTA reached the FIRST barrier
     a.n_params = h->n_params; a.n_mlp = h->n_mlp;
     a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
     a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
-    // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double; h->step is the step being applied
+    // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double
     a.n_steps = n_steps;
     for (uint32_t s = 0; s < n_steps && s < 4; ++s) {
-        a.ema_debias_old[s] = 1.0f - (float)pow((double)h->ema_decay, (double)(h->step + s - 1));
-        a.ema_debias_new[s] = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)(h->step + s)));
+        a.ema_debias_old[s] = 1.0f - (float)pow((double)h->ema_decay, (double)(first_step + s - 1));
+        a.ema_debias_new[s] = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)(first_step + s)));
     }
     a.apply = apply;
     a.timeline = h->timeline;
     a.perm_n = 0; a.perm_seed = 0; a.perm_base = 0;
-    a.dp_world = 1; a.dp_rank = 0; a.dp_step = h->step; a.x_stride = h->x_stride;
+    a.opt_step = first_step;
+    a.dp_world = 1; a.dp_rank = 0; a.dp_seq = h->dp_seq + 1; a.x_stride = h->x_stride;
+    a.error_flag = h->err_dev; a.dp_timeout_ms = h->dp_timeout_ms;
     if (apply && h->dp_world > 1) {
         a.dp_world = (uint32_t)h->dp_world; a.dp_rank = (uint32_t)h->dp_rank;
         for (int r = 0; r < h->dp_world; ++r) {
@@ -402,63 +488,73 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     }
     return a;
 }
+// Launches a step kernel and, on success, commits what it consumed: optimizer steps, grid-barrier arrivals, exchange steps.
+static int launch_and_commit(Net* h, const TrainArgs& a, uint32_t n_barriers) {
+    CU(launch_train_step(h->encoding, a, h->gm, h->stream));
+    h->launches += 1;
+    h->barrier_total += n_barriers * train_grid(a.n_local);
+    if (a.apply) {
+        h->step += a.n_steps;
+        if (a.dp_world > 1) h->dp_seq += a.n_steps;
+        h->pending_tiles = 0;
+    }
+    return NRC_B200_OK;
+}
+// Samples the loss of one step is normalised by.  A handle connected to data-parallel peers trains on the GLOBAL batch of
+// dp_world local batches whichever entry point is used (every rank must make the same calls).
+static uint32_t global_batch(const Net* h, uint32_t n_local) { return h->dp_world > 1 ? n_local * (uint32_t)h->dp_world : n_local; }
+static int read_loss(Net* h, const float* src_d, int n, float* loss_h) {   // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
+    CU(cudaMemcpyAsync(h->loss_pinned, src_d, 4 * n, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (*(volatile uint32_t*)h->err_host) return device_error(h);
+    float l = 0.0f;
+    for (int b = 0; b < n; ++b) l += h->loss_pinned[b];
+    *loss_h = l / (float)n;
+    return NRC_B200_OK;
+}
 
 int nrc_b200_train_grad(nrc_b200_handle h, const float* q, const float* t, uint32_t n_local, uint32_t n_global,
                         float** grad_d, void* cu_stream) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
     if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
         return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
-    h->barrier_total += train_grid(n_local);
-    CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/0), h->gm, h->stream));
-    h->launches += 1;
+    int rc = launch_and_commit(h, train_args(h, q, t, n_local, n_global, /*apply=*/0), 1);
+    if (rc != NRC_B200_OK) return rc;
     h->pending_tiles = n_local / 128;
     if (grad_d) *grad_d = h->grad_f32;
     return NRC_B200_OK;
 }
 
 int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (h->pending_tiles == 0) return fail(NRC_B200_ERR_INVALID, "train_apply without a pending gradient");
-    h->step += 1;
-    CU(launch_adam_ema(train_args(h, nullptr, nullptr, 0, 0, 1), h->stream));
+    TrainArgs a = train_args(h, nullptr, nullptr, 0, 0, 1);
+    a.dp_world = 1;                  // the caller has all-reduced grad_f32 itself
+    CU(launch_adam_ema(a, h->stream));
     h->launches += 1;
+    h->step += 1;
     h->pending_tiles = 0;
-    if (loss_h) {  // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
-        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        *loss_h = *h->loss_pinned;
-    }
+    if (loss_h) return read_loss(h, h->loss_d, 1, loss_h);
     return NRC_B200_OK;
 }
 
 int nrc_b200_train(nrc_b200_handle h, const float* q, const float* t, void* cu_stream, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;  // NRCNetwork.cu:43
+    ENTER(h);                        // NRCNetwork.cu:43
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
-    // one cooperative launch: forward + loss + backward + gradient reduction + Adam + EMA
-    h->step += 1;
-    h->barrier_total += NRC_B200_BATCH_SIZE / 128;
-    CU(launch_train_step(h->encoding, train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1), h->gm, h->stream));
-    h->launches += 1;
-    h->pending_tiles = 0;
-    if (loss_h) {  // Trainer::loss: D2H + stream sync (reduce_sum.h:146-149)
-        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        *loss_h = *h->loss_pinned;
-    }
+    // one cooperative launch: forward + loss + backward + gradient reduction (+ all-reduce over the peers) + Adam + EMA
+    int rc = launch_and_commit(h, train_args(h, q, t, NRC_B200_BATCH_SIZE, global_batch(h, NRC_B200_BATCH_SIZE), /*apply=*/1), 1);
+    if (rc != NRC_B200_OK) return rc;
+    if (loss_h) return read_loss(h, h->loss_d, 1, loss_h);
     return NRC_B200_OK;
 }
 
 // Host-buffer training step: H2D of one batch (983 KB + 197 KB) on the training stream, then the same kernels.
 int nrc_b200_train_host(nrc_b200_handle h, const float* q_h, const float* t_h, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (!q_h || !t_h) return fail(NRC_B200_ERR_INVALID, "null host buffer");
     if (!h->train_in_d) {
         CU(cudaMalloc(&h->train_in_d, (size_t)NRC_B200_BATCH_SIZE * 60));
@@ -471,8 +567,7 @@ int nrc_b200_train_host(nrc_b200_handle h, const float* q_h, const float* t_h, f
 
 // ---------------------------------------------------------------- data-parallel training over NVLink peer memory
 // Step 1 (every rank): allocate the exchange buffer and export its CUDA IPC handle (64 bytes).
-int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out) {
-    if (!h || h->destroyed || !ipc_handle_out) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+static int dp_alloc(Net* h) {
     CU(cudaStreamSynchronize(h->stream));
     dp_teardown(h);
     // per (parity, source rank) row: [(n_mlp + 1 -> 32) tagged float2 slots | n_grid floats]  (nrc_train.cu phase 3)
@@ -482,6 +577,14 @@ int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out) {
     CU(cudaMalloc(&h->dp_local, h->xbuf_bytes + flag_bytes));
     CU(cudaMemset(h->dp_local, 0, h->xbuf_bytes + flag_bytes));
     CU(cudaDeviceSynchronize());
+    h->dp_seq = 0;                   // tags / flags start at 1 on a zeroed buffer; never reset while connected (weights may be re-uploaded)
+    return NRC_B200_OK;
+}
+int nrc_b200_dp_export(nrc_b200_handle h, void* ipc_handle_out) {
+    if (!h || h->destroyed || !ipc_handle_out) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
+    DeviceGuard guard_(h->device);
+    int rc = dp_alloc(h);
+    if (rc != NRC_B200_OK) return rc;
     cudaIpcMemHandle_t mh;
     CU(cudaIpcGetMemHandle(&mh, h->dp_local));
     static_assert(sizeof(mh) == NRC_B200_IPC_HANDLE_BYTES, "IPC handle size");
@@ -494,6 +597,7 @@ int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_
     if (!h || h->destroyed || !ipc_handles) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
     if (world < 1 || world > kMaxDpRanks || rank < 0 || rank >= world) return fail(NRC_B200_ERR_INVALID, "bad rank/world");
     if (!h->dp_local) return fail(NRC_B200_ERR_INVALID, "nrc_b200_dp_export must be called first");
+    DeviceGuard guard_(h->device);
     for (int r = 0; r < world; ++r) {
         if (r == rank) { h->dp_peer[r] = h->dp_local; continue; }
         cudaIpcMemHandle_t mh;
@@ -503,27 +607,47 @@ int nrc_b200_dp_connect(nrc_b200_handle h, int rank, int world, const void* ipc_
     h->dp_rank = rank; h->dp_world = world;
     return NRC_B200_OK;
 }
+// Same exchange between handles of ONE process (one handle per GPU, driven from one or several host threads): peer
+// access instead of CUDA IPC.  handles[r] is rank r's handle; allocates every exchange buffer and connects all of them.
+int nrc_b200_dp_connect_local(nrc_b200_handle* handles, int world) {
+    if (!handles || world < 1 || world > kMaxDpRanks) return fail(NRC_B200_ERR_INVALID, "bad handles/world");
+    for (int r = 0; r < world; ++r) {
+        Net* h = handles[r];
+        if (!h || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle");
+        if (h->n_params != handles[0]->n_params) return fail(NRC_B200_ERR_INVALID, "handles must share one configuration");
+        DeviceGuard guard_(h->device);
+        int rc = dp_alloc(h);
+        if (rc != NRC_B200_OK) return rc;
+        for (int p = 0; p < world; ++p) {
+            if (handles[p]->device == h->device) continue;
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, h->device, handles[p]->device));
+            if (!can) return fail(NRC_B200_ERR_CUDA, "no peer access between the devices of the handles");
+            cudaError_t e = cudaDeviceEnablePeerAccess(handles[p]->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CU(e);
+            cudaGetLastError();
+        }
+    }
+    for (int r = 0; r < world; ++r) {
+        Net* h = handles[r];
+        for (int p = 0; p < world; ++p) h->dp_peer[p] = handles[p]->dp_local;
+        h->dp_rank = r; h->dp_world = world; h->dp_shared_process = true;
+    }
+    return NRC_B200_OK;
+}
 // One optimizer step on a global batch of n_global samples of which this rank holds n_local: ONE cooperative kernel
 // per rank does forward/backward, the gradient all-reduce (peer stores + flags over NVLink) and Adam + EMA.
 // Every rank must call it for every step; loss_h (optional, blocks) receives the global loss.
 int nrc_b200_train_dp(nrc_b200_handle h, const float* q, const float* t, uint32_t n_local, uint32_t n_global,
                       void* cu_stream, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
     if (n_local == 0 || n_local > NRC_B200_BATCH_SIZE || n_local % 128 != 0 || n_global < n_local)
         return fail(NRC_B200_ERR_INVALID, "n_local must be a positive multiple of 128, <= 16384 and <= n_global");
-    h->step += 1;
-    h->barrier_total += train_grid(n_local);
-    CU(launch_train_step(h->encoding, train_args(h, q, t, n_local, n_global, /*apply=*/1), h->gm, h->stream));
-    h->launches += 1;
-    h->pending_tiles = 0;
-    if (loss_h) {
-        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        *loss_h = *h->loss_pinned;
-    }
+    int rc = launch_and_commit(h, train_args(h, q, t, n_local, n_global, /*apply=*/1), 1);
+    if (rc != NRC_B200_OK) return rc;
+    if (loss_h) return read_loss(h, h->loss_d, 1, loss_h);
     return NRC_B200_OK;
 }
 
@@ -543,52 +667,39 @@ int nrc_b200_propagate_train_radiance(const nrc_b200_suffix_end_vertex* end_vert
     return NRC_B200_OK;
 }
 uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed) { return permute16(i & 0xFFFFu, seed); }
-// Device::nrcTrainRadiance (Device.cpp:1482-1513): NUM_BATCHES consecutive train() calls, as ONE cooperative launch.
-int nrc_b200_train_batches(nrc_b200_handle h, const float* q, const float* t, int n_batches, void* cu_stream, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
-    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
-    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
-    if (n_batches < 1 || n_batches > NRC_B200_NUM_BATCHES) return fail(NRC_B200_ERR_INVALID, "n_batches must be in [1, 4]");
-    if (h->dp_world > 1) return fail(NRC_B200_ERR_INVALID, "train_batches is single-GPU; use train_dp per batch");
+
+// n_batches consecutive optimizer steps on q + b*16384*15 / t + b*16384*3 (or, perm_n > 0, on the fused shuffle of the
+// frame's records), losses into loss4_d[b].  Frequency: ONE launch (MULTI instantiation, single GPU and data parallel);
+// Hash: one launch per batch (the grid scatter makes a step 4x longer and the in-kernel barriers cost more than the
+// launch gaps: 90 vs 76 us per step measured).
+static int train_steps(Net* h, const float* q, const float* t, int n_batches, uint32_t perm_n, uint32_t perm_seed) {
+    const uint32_t n_global = global_batch(h, NRC_B200_BATCH_SIZE);
     if (h->encoding == NRC_B200_HASH) {
-        // Hash: the grid scatter makes a step 4x longer and the in-kernel barriers cost more than the launch gaps
-        // (measured 90 vs 76 us per step): keep one launch per batch, losses into loss4_d[b].
         for (int b = 0; b < n_batches; ++b) {
-            h->step += 1;
-            h->barrier_total += NRC_B200_BATCH_SIZE / 128;
-            TrainArgs a = train_args(h, q + (size_t)b * NRC_B200_BATCH_SIZE * 15, t + (size_t)b * NRC_B200_BATCH_SIZE * 3,
-                                     NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1);
+            TrainArgs a = perm_n ? train_args(h, q, t, NRC_B200_BATCH_SIZE, n_global, 1)
+                                 : train_args(h, q + (size_t)b * NRC_B200_BATCH_SIZE * 15, t + (size_t)b * NRC_B200_BATCH_SIZE * 3,
+                                              NRC_B200_BATCH_SIZE, n_global, 1);
+            a.perm_n = perm_n; a.perm_seed = perm_seed; a.perm_base = (uint32_t)b * NRC_B200_BATCH_SIZE;
             a.loss_out = h->loss4_d + b;
-            CU(launch_train_step(h->encoding, a, h->gm, h->stream));
-            h->launches += 1;
-        }
-        h->pending_tiles = 0;
-        if (loss_h) {
-            CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 4 * n_batches, cudaMemcpyDeviceToHost, h->stream));
-            CU(cudaStreamSynchronize(h->stream));
-            float l = 0.0f;
-            for (int b = 0; b < n_batches; ++b) l += h->loss_pinned[b];
-            *loss_h = l / (float)n_batches;
+            int rc = launch_and_commit(h, a, 1);
+            if (rc != NRC_B200_OK) return rc;
         }
         return NRC_B200_OK;
     }
-    h->step += 1;
-    TrainArgs a = train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1, (uint32_t)n_batches);
-    a.barrier_target = h->barrier_total + NRC_B200_BATCH_SIZE / 128;
+    TrainArgs a = train_args(h, q, t, NRC_B200_BATCH_SIZE, n_global, 1, (uint32_t)n_batches);
+    a.perm_n = perm_n; a.perm_seed = perm_seed; a.perm_base = 0;
     a.loss_out = h->loss4_d;
-    h->barrier_total += (2 * n_batches - 1) * (NRC_B200_BATCH_SIZE / 128);
-    h->step += n_batches - 1;
-    CU(launch_train_step(h->encoding, a, h->gm, h->stream));
-    h->launches += 1;
-    h->pending_tiles = 0;
-    if (loss_h) {  // mean of the per-batch losses, as Device::nrcTrainRadiance reports it
-        CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 4 * n_batches, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        float l = 0.0f;
-        for (int b = 0; b < n_batches; ++b) l += h->loss_pinned[b];
-        *loss_h = l / (float)n_batches;
-    }
+    return launch_and_commit(h, a, 2 * (uint32_t)n_batches - 1);
+}
+// Device::nrcTrainRadiance (Device.cpp:1482-1513): NUM_BATCHES consecutive train() calls.
+int nrc_b200_train_batches(nrc_b200_handle h, const float* q, const float* t, int n_batches, void* cu_stream, float* loss_h) {
+    ENTER(h);
+    if (cu_stream) h->stream = (cudaStream_t)cu_stream;
+    if (!q || !t) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    if (n_batches < 1 || n_batches > NRC_B200_NUM_BATCHES) return fail(NRC_B200_ERR_INVALID, "n_batches must be in [1, 4]");
+    int rc = train_steps(h, q, t, n_batches, 0, 0);
+    if (rc != NRC_B200_OK) return rc;
+    if (loss_h) return read_loss(h, h->loss4_d, n_batches, loss_h);   // mean of the per-batch losses, as Device::nrcTrainRadiance reports it
     return NRC_B200_OK;
 }
 int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
@@ -599,6 +710,15 @@ int nrc_b200_permute_train_data(const float* q_src_d, const float* t_src_d, floa
     CU(launch_permute(q_src_d, t_src_d, q_dst_d, t_dst_d, (uint32_t)n, seed, (cudaStream_t)cu_stream));
     return NRC_B200_OK;
 }
+// permute_train_data with a caller-supplied permutation (the reference's cuRAND + CUB result, nrc_helpers.cu:226-249).
+int nrc_b200_permute_train_data_with(const float* q_src_d, const float* t_src_d, float* q_dst_d, float* t_dst_d,
+                                     const int* permutation_d, int num_records, void* cu_stream) {
+    if (!q_src_d || !t_src_d || !q_dst_d || !t_dst_d || !permutation_d) return fail(NRC_B200_ERR_INVALID, "null device buffer");
+    const int n = std::min(num_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
+    if (n <= 0) return NRC_B200_OK;
+    CU(launch_permute_with(q_src_d, t_src_d, q_dst_d, t_dst_d, permutation_d, (uint32_t)n, (cudaStream_t)cu_stream));
+    return NRC_B200_OK;
+}
 void nrc_b200_adjust_tile_size(int tile_x, int tile_y, int num_train_records, int* new_x, int* new_y) {
     // Device::adjustTileSize, Device.cpp:818-828
     const float ratio = (float)(num_train_records * 1.25f) / (float)(NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
@@ -607,34 +727,21 @@ void nrc_b200_adjust_tile_size(int tile_x, int tile_y, int num_train_records, in
     if (new_y) *new_y = std::max((int)(tile_y * r + 0.5f), 2);
 }
 
-static int train_shuffled_impl(Net* h, const float* q, const float* t, uint32_t n, uint32_t seed, uint32_t batch, float* loss_slot) {
-    h->step += 1;
-    h->barrier_total += NRC_B200_BATCH_SIZE / 128;
-    TrainArgs a = train_args(h, q, t, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, /*apply=*/1);
-    a.perm_n = n; a.perm_seed = seed; a.perm_base = batch * NRC_B200_BATCH_SIZE;
-    if (loss_slot) a.loss_out = loss_slot;
-    CU(launch_train_step(h->encoding, a, h->gm, h->stream));
-    h->launches += 1;
-    return NRC_B200_OK;
-}
 // permute_train_data + Network::train on batch `batch_index` in one launch: the training kernel's loader gathers
 // src[permutation(d) % num_records] itself.
 int nrc_b200_train_shuffled(nrc_b200_handle h, const float* q_src_d, const float* t_src_d, int num_records, uint32_t seed,
                             uint32_t batch_index, void* cu_stream, float* loss_h) {
-    if (!h) return fail(NRC_B200_ERR_INVALID, "null handle");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     if (!q_src_d || !t_src_d) return fail(NRC_B200_ERR_INVALID, "null device buffer");
     if (batch_index >= NRC_B200_NUM_BATCHES) return fail(NRC_B200_ERR_INVALID, "batch_index must be < 4");
     const int n = std::min(num_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
     if (n <= 0) return NRC_B200_OK;
-    int rc = train_shuffled_impl(h, q_src_d, t_src_d, (uint32_t)n, seed, batch_index, nullptr);
+    TrainArgs a = train_args(h, q_src_d, t_src_d, NRC_B200_BATCH_SIZE, global_batch(h, NRC_B200_BATCH_SIZE), /*apply=*/1);
+    a.perm_n = (uint32_t)n; a.perm_seed = seed; a.perm_base = batch_index * NRC_B200_BATCH_SIZE;
+    int rc = launch_and_commit(h, a, 1);
     if (rc != NRC_B200_OK) return rc;
-    if (loss_h) {
-        CU(cudaMemcpyAsync(h->loss_pinned, h->loss_d, 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
-        *loss_h = *h->loss_pinned;
-    }
+    if (loss_h) return read_loss(h, h->loss_d, 1, loss_h);
     return NRC_B200_OK;
 }
 
@@ -642,8 +749,8 @@ int nrc_b200_train_shuffled(nrc_b200_handle h, const float* q_src_d, const float
 // 4 x train.  No host synchronisation unless stat != NULL (then one read-back of the four losses at the end; the
 // reference synchronises after every training step).
 int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream, nrc_b200_training_stat* stat) {
-    if (!h || !f) return fail(NRC_B200_ERR_INVALID, "null argument");
-    if (h->destroyed) return NRC_B200_ERR_DESTROYED;
+    if (!f) return fail(NRC_B200_ERR_INVALID, "null argument");
+    ENTER(h);
     if (cu_stream) h->stream = (cudaStream_t)cu_stream;
     const bool skip_render_cache = f->render_mode == 1 || f->render_mode == 3;   // NoCache, CacheFirstVertex
     const float* q = f->queries_d;
@@ -656,38 +763,21 @@ int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream,
     if (!skip_render_cache && f->throughput_d && f->output_rgba_d)
         acc = AccumArgs{f->throughput_d, reinterpret_cast<float4*>(f->output_rgba_d), f->num_pixels, f->render_mode,
                         1.0f / (float)(f->iteration_index + 1)};
-    CU(launch_infer(h->encoding, q, r, n, h->ema, h->gm, h->num_sms, h->stream, &acc));
+    CU(run_infer(h, q, r, n, h->stream, &acc));
     h->launches += 1;
     const int n_rec = std::min(f->num_train_records, NRC_B200_BATCH_SIZE * NRC_B200_NUM_BATCHES);
     if (stat) { stat->loss = 0.0f; stat->num_train_records = n_rec; }
     if (n_rec > 0) {
+        if (!f->train_queries_d || !f->train_targets_d) return fail(NRC_B200_ERR_INVALID, "null training buffer");
         if (f->end_vertices_d && f->records_d && f->num_tiles) {                   // nrcPropagateRadiance
             CU(launch_propagate(f->end_vertices_d, f->results_d + (size_t)f->num_pixels * 3, f->records_d, f->train_targets_d,
                                 f->num_tiles, h->stream));
             h->launches += 1;
         }
-        if (h->dp_world > 1 || h->encoding == NRC_B200_HASH) {
-            for (uint32_t b = 0; b < NRC_B200_NUM_BATCHES; ++b) {                   // nrcShuffleTrainingData + nrcTrainRadiance
-                int rc = train_shuffled_impl(h, f->train_queries_d, f->train_targets_d, (uint32_t)n_rec, f->shuffle_seed, b, h->loss4_d + b);
-                if (rc != NRC_B200_OK) return rc;
-            }
-        } else {                                                     // Frequency: the four steps in one launch
-            h->step += 1;
-            TrainArgs a = train_args(h, f->train_queries_d, f->train_targets_d, NRC_B200_BATCH_SIZE, NRC_B200_BATCH_SIZE, 1,
-                                     NRC_B200_NUM_BATCHES);
-            a.barrier_target = h->barrier_total + NRC_B200_BATCH_SIZE / 128;
-            a.perm_n = (uint32_t)n_rec; a.perm_seed = f->shuffle_seed; a.perm_base = 0;
-            a.loss_out = h->loss4_d;
-            h->barrier_total += (2 * NRC_B200_NUM_BATCHES - 1) * (NRC_B200_BATCH_SIZE / 128);
-            h->step += NRC_B200_NUM_BATCHES - 1;
-            CU(launch_train_step(h->encoding, a, h->gm, h->stream));
-            h->launches += 1;
-        }
-        if (stat) {
-            CU(cudaMemcpyAsync(h->loss_pinned, h->loss4_d, 16, cudaMemcpyDeviceToHost, h->stream));
-            CU(cudaStreamSynchronize(h->stream));
-            stat->loss = (h->loss_pinned[0] + h->loss_pinned[1] + h->loss_pinned[2] + h->loss_pinned[3]) * (1.0f / NRC_B200_NUM_BATCHES);
-        }
+        // nrcShuffleTrainingData + nrcTrainRadiance: the four steps with the shuffle fused into their loaders
+        int rc = train_steps(h, f->train_queries_d, f->train_targets_d, NRC_B200_NUM_BATCHES, (uint32_t)n_rec, f->shuffle_seed);
+        if (rc != NRC_B200_OK) return rc;
+        if (stat) return read_loss(h, h->loss4_d, NRC_B200_NUM_BATCHES, &stat->loss);
     }
     return NRC_B200_OK;
 }
@@ -696,9 +786,10 @@ int nrc_b200_update(nrc_b200_handle h, const nrc_b200_frame* f, void* cu_stream,
 // 0 start, 1 encoded, 2 forward done, 3 backward + weight gradients done, 4 partials stored, 5 past the grid barrier, 6 end.
 int nrc_b200_debug_train_timeline(nrc_b200_handle h, int enable, long long* dst_host) {
     if (!h || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle");
+    DeviceGuard guard_(h->device);
     if (enable && !h->timeline) {
-        CU(cudaMalloc(&h->timeline, 128 * 8 * sizeof(long long)));
-        CU(cudaMemset(h->timeline, 0, 128 * 8 * sizeof(long long)));
+        CU(cudaMalloc(&h->timeline, 148 * 8 * sizeof(long long)));
+        CU(cudaMemset(h->timeline, 0, 148 * 8 * sizeof(long long)));
     }
     if (dst_host && h->timeline) {
         CU(cudaStreamSynchronize(h->stream));

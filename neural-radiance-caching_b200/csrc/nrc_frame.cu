@@ -69,6 +69,20 @@ nrc_permute_kernel(const float* __restrict__ q_src, const float* __restrict__ t_
     else t_dst[d * 3u + (c - 15u)] = __ldg(t_src + (size_t)s * 3u + (c - 15u));
 }
 
+// The same gather with a caller-supplied permutation (the reference's cuRAND keys + CUB radix sort, NRCUtil.cu:20-35):
+// permute_train_data of nrc_helpers.cu:226-249 argument for argument.
+__global__ void __launch_bounds__(256)
+nrc_permute_with_kernel(const float* __restrict__ q_src, const float* __restrict__ t_src, float* __restrict__ q_dst,
+                        float* __restrict__ t_dst, const int* __restrict__ permutation, uint32_t num_records) {
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;   // 0 .. 65536*18
+    if (e >= 65536u * 18u) return;
+    const uint32_t d = e / 18u, c = e - d * 18u;
+    const int s = __ldg(permutation + d) % (int)num_records;   // signed modulo, as the reference computes it
+    if (s < 0) return;
+    if (c < 15u) q_dst[d * 15u + c] = __ldg(q_src + (size_t)s * 15u + c);
+    else t_dst[d * 3u + (c - 15u)] = __ldg(t_src + (size_t)s * 3u + (c - 15u));
+}
+
 cudaError_t launch_accumulate(const float* radiance, const float* throughput, float* out4, uint32_t n_pixels, int mode,
                               uint32_t iteration_index, cudaStream_t stream) {
     if (n_pixels == 0) return cudaSuccess;
@@ -86,6 +100,12 @@ cudaError_t launch_propagate(const void* end_vertices, const float* end_radiance
 cudaError_t launch_permute(const float* q_src, const float* t_src, float* q_dst, float* t_dst, uint32_t num_records,
                            uint32_t seed, cudaStream_t stream) {
     nrc_permute_kernel<<<(65536u * 18u + 255) / 256, 256, 0, stream>>>(q_src, t_src, q_dst, t_dst, num_records, seed);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_permute_with(const float* q_src, const float* t_src, float* q_dst, float* t_dst, const int* permutation,
+                                uint32_t num_records, cudaStream_t stream) {
+    nrc_permute_with_kernel<<<(65536u * 18u + 255) / 256, 256, 0, stream>>>(q_src, t_src, q_dst, t_dst, permutation, num_records);
     return cudaGetLastError();
 }
 

@@ -55,30 +55,18 @@ struct InferSmem {
     static constexpr int kTotal = kAccOff + kGroups * 2 * kAcc;
 };
 
-// Copies one row-major fp16 matrix W[n_out][n_in] into the UMMA K-major interleaved image:
-// off(o,k) = (k/8)*(n_out*16) + (o/8)*128 + (o%8)*16 + (k%8)*2     (8x8 core matrices, 128 B each)
-__device__ __forceinline__ void stage_weight(uint8_t* dst, const __half* __restrict__ W, int n_out, int n_in, int tid,
-                                             int nthr) {
-    const int chunks = n_in / 8;
-    for (int i = tid; i < n_out * chunks; i += nthr) {
-        const int o = i / chunks, c = i - o * chunks;
-        const uint4 v = *reinterpret_cast<const uint4*>(W + (size_t)o * n_in + c * 8);
-        *reinterpret_cast<uint4*>(dst + c * (n_out * 16) + (o >> 3) * 128 + (o & 7) * 16) = v;
-    }
-}
-
 // Named barriers of group g (128 threads each): 1 + g "A operand ready", 1 + kGroups + g "accumulator ready" / group sync.
 __device__ __forceinline__ void bar_sync_id(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
 __device__ __forceinline__ void bar_arrive_id(int id) { asm volatile("bar.arrive %0, 128;" ::"r"(id) : "memory"); }
 
 // One layer of the group's tile, issued by a single elected lane.  LY is a compile-time constant so every descriptor is
 // a uniform-register immediate offset and ptxas emits back-to-back UTCHMMA.
-template <int ENC, int LY>
+template <int ENC, bool ACC16, int LY>
 __device__ __forceinline__ void issue_layer(uint32_t sbase, uint32_t a0, uint32_t dD, uint64_t* d_ready) {
     constexpr int E = ENC == 0 ? 80 : 64;
     using L = InferSmem<E>;
-    constexpr uint32_t idesc64 = umma_idesc_f16(128, 64, 0, 0);
-    constexpr uint32_t idesc16 = umma_idesc_f16(128, 16, 0, 0);
+    constexpr uint32_t idesc64 = ACC16 ? umma_idesc_f16_acc16(128, 64, 0, 0) : umma_idesc_f16(128, 64, 0, 0);
+    constexpr uint32_t idesc16 = ACC16 ? umma_idesc_f16_acc16(128, 16, 0, 0) : umma_idesc_f16(128, 16, 0, 0);
     const uint32_t dA = dD + kTmemA;
     if constexpr (LY == 0) {
         const uint64_t d_a0 = umma_desc(a0, 2048, 128);   // K-major A [128 x E]: +4096 B per k-step
@@ -100,10 +88,12 @@ __device__ __forceinline__ void issue_layer(uint32_t sbase, uint32_t a0, uint32_
     umma_commit(d_ready);
 }
 
-template <int ENC>  // 0 = Frequency (E = 80), 1 = Hash (E = 64)
+// ENC: 0 = Frequency (E = 80), 1 = Hash (E = 64).  ACC16: fp16 accumulators (one fp16 per 32-bit TMEM column, rounded after
+// every K = 16 instruction: the arithmetic of the reference's wmma::accumulator<__half>, fully_fused_mlp.cu:68) instead of fp32.
+template <int ENC, bool ACC16>
 __global__ void __launch_bounds__(kThreads, 1)
 nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t n, const __half* __restrict__ params,
-                 GridMeta gm, AccumArgs acc) {
+                 const __half* __restrict__ w_img, GridMeta gm, AccumArgs acc) {
     constexpr int E = ENC == 0 ? 80 : 64;
     using L = InferSmem<E>;
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -111,7 +101,8 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     uint64_t* in_full = bars;              // [kGroups] raw tile landed in smem
     uint64_t* d_ready = bars + kGroups;    // [kGroups] accumulator complete
     uint64_t* acc_full = bars + 2 * kGroups;   // [kGroups] throughput + output rows of the tile landed (pipelined loop)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGroups);
+    uint64_t* w_full = bars + 3 * kGroups;     // the weight image landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 * kGroups + 1);
 
     // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything derived from it (TMEM
     // addresses, barrier ids, shared-memory bases of the group) in uniform registers instead of R2UR moves per use
@@ -119,20 +110,17 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
     const uint32_t tile_stride = gridDim.x * kGroups;
 
-    // ---- one-time setup: weights -> smem images, barriers, TMEM
-    {
-        const __half* W = params;
-        stage_weight(smem, W, 64, E, tid, kThreads);
-        W += 64 * E;
-        for (int l = 0; l < 4; ++l, W += 4096) stage_weight(smem + L::kWin + l * 8192, W, 64, 64, tid, kThreads);
-        stage_weight(smem + L::kWin + L::kWhid, W, 16, 64, tid, kThreads);
-    }
+    // ---- one-time setup: barriers, TMEM, and ONE bulk copy (UBLKCP) of the weights: w_img is the UMMA K-major image of the
+    //      six matrices (off(o,k) = (k/8)*(n_out*16) + (o/8)*128 + (o%8)*16 + (k%8)*2 per matrix), kept current in global
+    //      memory by the optimizer phase of the training kernel, so no CTA re-formats the 45 KB with generic loads.
     if (tid == 0) {
         for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&d_ready[g], 1); mbar_init(&acc_full[g], 1); }
+        mbar_init(w_full, 1);
         fence_mbar_init();
+        mbar_arrive_expect_tx(w_full, L::kWeights);
+        bulk_g2s(smem, w_img, L::kWeights, w_full);
     }
     if (warp == 0) tmem_alloc(tmem_slot, 512);
-    fence_proxy_async_smem();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -192,7 +180,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             if ((warp & 3) == 0) {
                 bar_sync_id(bar_a);
                 tc_fence_after();
-                if (elect_one()) issue_layer<ENC, decltype(LY)::value>(sbase, a0, dD, &d_ready[g]);
+                if (elect_one()) issue_layer<ENC, ACC16, decltype(LY)::value>(sbase, a0, dD, &d_ready[g]);
                 __syncwarp();
                 overlap();
                 mbar_wait(&d_ready[g], ph_d);
@@ -216,7 +204,10 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 tmem_wait_ld();
                 if (pc < 3) tmem_ld16(tD + (pc + 1) * 16, v[(pc + 1) & 1]);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) w[i] = pack_relu_h2(__uint_as_float(v[pc & 1][2 * i]), __uint_as_float(v[pc & 1][2 * i + 1]));
+                for (int i = 0; i < 8; ++i) {
+                    if constexpr (ACC16) w[i] = relu_h2(__byte_perm(v[pc & 1][2 * i], v[pc & 1][2 * i + 1], 0x5410));   // fp16 in the low halves
+                    else w[i] = pack_relu_h2(__uint_as_float(v[pc & 1][2 * i]), __uint_as_float(v[pc & 1][2 * i + 1]));
+                }
                 tmem_st8(tA + pc * 8, w);
             }
         };
@@ -230,7 +221,10 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             tmem_ld4(tD, v);
             tmem_wait_ld();
 #pragma unroll
-            for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
+            for (int c = 0; c < 3; ++c) {
+                if constexpr (ACC16) y[c] = fmaxf(__half2float(__ushort_as_half((unsigned short)(v[c] & 0xFFFFu))), 0.0f);
+                else y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
+            }
             // D is drained: the next tile's first run_layer orders this read before the MMA that overwrites it.
         };
         auto emit_tile = [&](uint32_t t, const uint8_t* staged, const float (&y)[3]) {
@@ -275,7 +269,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             emit_tile(t, staged, y);
         };
 
-        uint32_t t = blockIdx.x * kGroups + g;
+        // tile t of round r belongs to group g of CTA b with t = r*stride + g*gridDim + b: the tiles of the last (partial) round
+        // land on DIFFERENT SMs (one group each, which then has the SM to itself) instead of filling a few SMs five deep
+        uint32_t t = g * gridDim.x + blockIdx.x;
         uint32_t ph_in = 0;
         if constexpr (NRC_INFER_PIPELINE && L::kA0 != 0) {
             // ---- Frequency: the encoding of tile t + stride is cut into five slices that run while the tensor pipe works on
@@ -312,6 +308,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 encode_frequency_slice<0>(q, a_row); encode_frequency_slice<1>(q, a_row); encode_frequency_slice<2>(q, a_row);
                 encode_frequency_slice<3>(q, a_row); encode_frequency_slice<4>(q, a_row);
             }
+            if ((warp & 3) == 0) mbar_wait(w_full, 0);   // issuing warp: the weight image has landed (async-proxy write -> async-proxy read)
             for (; t < n_tiles; t += tile_stride) {
                 const bool has_next = t + tile_stride < n_tiles;
                 run_layer(std::integral_constant<int, 0>{}, [&] { if (has_next) read_q(); });   // raw queries of the next tile -> registers
@@ -334,6 +331,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         } else {
         uint32_t par = 0;
         if (t < n_tiles) load_tile(t, 0);
+        if ((warp & 3) == 0) mbar_wait(w_full, 0);       // issuing warp: the weight image has landed
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
             float q[15];
@@ -378,28 +376,33 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
     if (warp == 0) tmem_dealloc(tmem_base, 512);
 }
 
-template <int ENC>
-static cudaError_t launch_infer_t(const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
+template <int ENC, bool ACC16>
+static cudaError_t launch_infer_t(const float* in, float* out, uint32_t n, const __half* params, const __half* w_img, const GridMeta& gm,
                                   int num_sms, cudaStream_t stream, const AccumArgs& acc) {
     using L = InferSmem<ENC == 0 ? 80 : 64>;
-    static bool configured[2] = {false, false};
-    if (!configured[ENC]) {
-        cudaError_t e = cudaFuncSetAttribute(nrc_infer_kernel<ENC>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
-        if (e != cudaSuccess) return e;
-        configured[ENC] = true;
-    }
     const uint32_t n_tiles = (n + kTile - 1) / kTile;
     const uint32_t grid = min((uint32_t)num_sms, (n_tiles + kGroups - 1) / kGroups);
-    nrc_infer_kernel<ENC><<<grid, kThreads, acc.out ? L::kTotal : L::kTotalNoAcc, stream>>>(in, out, n, params, gm, acc);
+    nrc_infer_kernel<ENC, ACC16><<<grid, kThreads, acc.out ? L::kTotal : L::kTotalNoAcc, stream>>>(in, out, n, params, w_img, gm, acc);
     return cudaGetLastError();
 }
 
-cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
-                         int num_sms, cudaStream_t stream, const AccumArgs* acc) {
+cudaError_t configure_infer_kernels() {   // per device (the attribute is not per process): called when a handle is created
+    cudaError_t e = cudaFuncSetAttribute(nrc_infer_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, InferSmem<80>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_infer_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, InferSmem<80>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_infer_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, InferSmem<64>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_infer_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, InferSmem<64>::kTotal);
+    return e;
+}
+
+cudaError_t launch_infer(int encoding, int acc16, const float* in, float* out, uint32_t n, const __half* params, const __half* w_img,
+                         const GridMeta& gm, int num_sms, cudaStream_t stream, const AccumArgs* acc) {
     if (n == 0) return cudaSuccess;
     const AccumArgs a = acc ? *acc : AccumArgs{nullptr, nullptr, 0, 0, 0.0f};
-    return encoding == 0 ? launch_infer_t<0>(in, out, n, params, gm, num_sms, stream, a)
-                         : launch_infer_t<1>(in, out, n, params, gm, num_sms, stream, a);
+    if (encoding == 0)
+        return acc16 ? launch_infer_t<0, true>(in, out, n, params, w_img, gm, num_sms, stream, a)
+                     : launch_infer_t<0, false>(in, out, n, params, w_img, gm, num_sms, stream, a);
+    return acc16 ? launch_infer_t<1, true>(in, out, n, params, w_img, gm, num_sms, stream, a)
+                 : launch_infer_t<1, false>(in, out, n, params, w_img, gm, num_sms, stream, a);
 }
 
 }  // namespace nrcb

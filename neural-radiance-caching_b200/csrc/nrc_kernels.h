@@ -17,8 +17,14 @@ struct AccumArgs {
     int mode;                  // nrc::RenderMode
     float weight;              // 1 / (iterationIndex + 1)
 };
-cudaError_t launch_infer(int encoding, const float* in, float* out, uint32_t n, const __half* params, const GridMeta& gm,
-                         int num_sms, cudaStream_t stream, const AccumArgs* acc = nullptr);
+// params: fp16 parameter vector (the grid part is read from it); w_img: UMMA shared-memory image of its MLP part
+// (brought in with one bulk copy per CTA).  acc16 = 1: fp16 accumulators (the arithmetic of the reference's
+// wmma::accumulator<__half> fragments, fully_fused_mlp.cu:68) instead of fp32.
+cudaError_t launch_infer(int encoding, int acc16, const float* in, float* out, uint32_t n, const __half* params, const __half* w_img,
+                         const GridMeta& gm, int num_sms, cudaStream_t stream, const AccumArgs* acc = nullptr);
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device: called for the current device when a handle is created.
+cudaError_t configure_infer_kernels();
+cudaError_t configure_train_kernels();
 
 // nrc_train.cu -- ONE cooperative kernel per optimizer step:
 //   phase 1  per 128-sample tile: encodings, forward, loss, backward, per-tile weight gradients (tcgen05)
@@ -30,7 +36,7 @@ struct TrainArgs {
     const float* in; const float* targets;
     uint32_t n_local, n_global;      // samples of this launch / of the global batch (loss normalisation)
     // parameter block
-    float* master; __half* params; __half* params_img; __half* ema; __half* grads;
+    float* master; __half* params; __half* params_img; __half* ema; __half* ema_img; __half* grads;
     float* m1; float* m2; uint32_t* steps;
     // scratch
     float* partials;                 // [n_tiles][n_mlp] per-tile weight-gradient partials (loss-scaled)
@@ -44,7 +50,7 @@ struct TrainArgs {
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
     float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
     int apply;
-    // n_steps optimizer steps in ONE launch (apply = 1, dp_world = 1): step s trains on samples [s*n_local, (s+1)*n_local)
+    // n_steps optimizer steps in ONE launch (apply = 1): step s trains on samples [s*n_local, (s+1)*n_local)
     // of `in` / `targets` (fused shuffle: destination indices perm_base + s*n_local + ...), writes its loss to
     // loss_out[s]; two grid barriers per step (gradients complete / weights updated), the last one omitted.
     uint32_t n_steps;
@@ -58,9 +64,14 @@ struct TrainArgs {
     // Fused shuffle (perm_n > 0): sample d = perm_base + tile*128 + row reads record permute16(d, perm_seed) % perm_n
     // of `in` / `targets` (the reference's permute_train_data, nrc_helpers.cu:226-249, without the 4.7 MB copy).
     uint32_t perm_n, perm_seed, perm_base;
-    uint32_t dp_world, dp_rank, dp_step, x_stride;
+    uint32_t opt_step;               // number of the (first) optimizer step of this launch: 1, 2, ... (Adam/EMA bias corrections)
+    uint32_t dp_world, dp_rank, x_stride;
+    uint32_t dp_seq;                 // exchange sequence number of the (first) step: tag / flag value and buffer parity; counts
+                                     // from 1 since the buffers were connected and is never reset (weights may be re-uploaded)
     float* xbuf[8];
     uint32_t* xflag[8];
+    uint32_t* error_flag;            // host-mapped word: a peer that stays silent for dp_timeout_ms raises it (no trap: the
+    uint32_t dp_timeout_ms;          // context survives, the next API call reports the error)
 };
 constexpr int kMaxDpRanks = 8;
 // CTAs of a step launch: one per 128-sample tile, but never fewer than 128 -- short data-parallel shards keep the gradient
@@ -81,5 +92,7 @@ cudaError_t launch_propagate(const void* end_vertices, const float* end_radiance
                              uint32_t n_tiles, cudaStream_t stream);
 cudaError_t launch_permute(const float* q_src, const float* t_src, float* q_dst, float* t_dst, uint32_t num_records,
                            uint32_t seed, cudaStream_t stream);
+cudaError_t launch_permute_with(const float* q_src, const float* t_src, float* q_dst, float* t_dst, const int* permutation,
+                                uint32_t num_records, cudaStream_t stream);
 
 }  // namespace nrcb

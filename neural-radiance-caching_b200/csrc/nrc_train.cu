@@ -124,10 +124,13 @@ __device__ __forceinline__ void adam_ema_matrix_param(const TrainArgs& a, uint32
     a.master[i] = new_weight;
     const __half w_half = __float2half_rn(new_weight);
     a.params[i] = w_half;
-    a.params_img[img_index(i, E)] = w_half;
+    const uint32_t img = img_index(i, E);
+    a.params_img[img] = w_half;
     const float old_part = __fmul_rn(__fmul_rn(__half2float(p.ema), a.ema_decay), a.ema_debias_old[s]);
     const float filtered = __fmul_rn(fmaf(__half2float(w_half), 1.0f - a.ema_decay, old_part), a.ema_debias_new[s]);
-    a.ema[i] = __float2half_rn(filtered);
+    const __half e_half = __float2half_rn(filtered);
+    a.ema[i] = e_half;
+    a.ema_img[img] = e_half;        // the query kernel bulk-copies this image instead of re-formatting the weights per CTA
 }
 
 // ---------------------------------------------------------------- optimizer (per parameter)
@@ -159,6 +162,7 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
     const float filtered = (__half2float(a.ema[i]) * a.ema_decay * a.ema_debias_old[s] +
                             __half2float(w_half) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
     a.ema[i] = __float2half_rn(filtered);
+    if (is_matrix) a.ema_img[img_index(i, E)] = __float2half_rn(filtered);
 }
 
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
@@ -170,7 +174,7 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
     // The bias-corrected learning rate depends on the parameter's own step count only; almost every touched entry has
     // been touched in every step so far, so the two powf of that common count are evaluated once per thread.
     // (evaluated after the first group of loads has been issued, so it overlaps their latency)
-    const uint32_t common = a.dp_step + s;
+    const uint32_t common = a.opt_step + s;
     float lr_common = 0.0f;
     bool have_lr = false;
     for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 8 * kTrainThreads) {
@@ -714,13 +718,30 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             }
         } else {
             // ---- data parallel: the all-reduce happens here, over NVLink peer memory.
-            // MLP slice + loss use a low-latency protocol: every 8-byte store carries (value, step tag), so the
+            // MLP slice + loss use a low-latency protocol: every 8-byte store carries (value, sequence tag), so the
             // receiver polls the data words themselves -- no fence, no separate flag, one NVLink one-way latency.
             // The (large) grid part is pushed as plain floats, then fence + one flag per slice.
-            const uint32_t par = a.dp_step & 1;
+            // seq = exchange sequence number of this step (monotonic since the buffers were connected, independent of the
+            // optimizer step counter, which a weight upload resets); buffers double-buffered by its parity.
+            const uint32_t seq = a.dp_seq + s;
+            const uint32_t par = seq & 1;
             const uint32_t LLS = (NMLP + 1 + 31) & ~31u;                        // float2 slots of the tagged region
             auto row = [&](uint32_t dst, uint32_t src) { return a.xbuf[dst] + ((size_t)par * R + src) * a.x_stride; };
-            const float tag = __uint_as_float(a.dp_step);
+            const float tag = __uint_as_float(seq);
+            // A silent peer must not take the context down: after dp_timeout_ms the waiting thread raises the host-mapped
+            // error word (the next API call on the handle reports it) and gives up; the step's result is then undefined.
+            auto timed_out = [&](uint32_t& spins, unsigned long long& t0) {
+                if ((++spins & 1023u) != 0) return false;
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0) { t0 = now; return false; }
+                if (now - t0 > (unsigned long long)a.dp_timeout_ms * 1000000ull || *(volatile uint32_t*)a.error_flag != 0) {
+                    *(volatile uint32_t*)a.error_flag = seq;
+                    __threadfence_system();
+                    return true;
+                }
+                return false;
+            };
             float g_mine[2] = {0.0f, 0.0f};                                       // <= 2 slice elements per thread
             for (uint32_t j = tid, u = 0; j < hi - lo; j += kTrainThreads, ++u) {
                 const float g = slice_grad(j);
@@ -748,39 +769,40 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 __syncthreads();
                 if ((uint32_t)tid < R && (uint32_t)tid != me) {
                     uint32_t* f = a.xflag[tid] + ((size_t)par * R + me) * 128 + tile;
-                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(a.dp_step) : "memory");
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(seq) : "memory");
                 }
             }
             auto poll = [&](const float2* p) {      // tagged word of a peer for this step
                 float2 v;
                 uint32_t spins = 0;
-                do {
+                unsigned long long t0 = 0;
+                for (;;) {
                     asm volatile("ld.relaxed.sys.global.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p) : "memory");
-                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-                } while (__float_as_uint(v.y) != a.dp_step);
-                return v.x;
+                    if (__float_as_uint(v.y) == seq) return v.x;
+                    if (timed_out(spins, t0)) return 0.0f;
+                }
             };
             for (uint32_t j = tid, u = 0; j < hi - lo; j += kTrainThreads, ++u) {
                 float g = 0.0f;
                 for (uint32_t r = 0; r < R; ++r)     // rank order: identical sums on every rank
                     g += (r == me && u < 2) ? g_mine[u] : poll(reinterpret_cast<const float2*>(row(me, r)) + lo + j);
                 a.grad_f32[lo + j] = g;
-                if (pre_ok) adam_ema_matrix_param(a, lo + j, g, E, 0, pst);
-                else adam_ema_param(a, lo + j, g, E);
+                if (pre_ok) adam_ema_matrix_param(a, lo + j, g, E, s, pst);
+                else adam_ema_param(a, lo + j, g, E, s);
             }
             if (tile == 0 && tid == 0) {
                 float l = 0.0f;
                 for (uint32_t r = 0; r < R; ++r) l += r == me ? l_mine : poll(reinterpret_cast<const float2*>(row(me, r)) + NMLP);
-                *a.loss_out = l;
+                a.loss_out[s] = l;
             }
             if constexpr (ENC == 1) {
                 if ((uint32_t)tid < R && (uint32_t)tid != me) {
                     const uint32_t* w = a.xflag[me] + ((size_t)par * R + tid) * 128 + tile;
                     uint32_t seen, spins = 0;
+                    unsigned long long t0 = 0;
                     do {
                         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(w) : "memory");
-                        if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-                    } while ((int32_t)(seen - a.dp_step) < 0);
+                    } while ((int32_t)(seen - seq) < 0 && !timed_out(spins, t0));
                 }
                 __syncthreads();
                 grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) {   // rank order: identical sums on every rank
@@ -837,19 +859,19 @@ nrc_make_image_kernel(const __half* __restrict__ params, __half* __restrict__ im
 }
 
 // ---------------------------------------------------------------- launchers
+cudaError_t configure_train_kernels() {   // per device (the attribute is not per process): called when a handle is created
+    cudaError_t e = cudaFuncSetAttribute(nrc_train_step_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrainSmem<80>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_train_step_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrainSmem<80>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_train_step_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrainSmem<64>::kTotal);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_train_step_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TrainSmem<64>::kTotal);
+    return e;
+}
 template <int ENC>
 static cudaError_t launch_train_t(const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
     using L = TrainSmem<ENC == 0 ? 80 : 64>;
-    static bool configured[2] = {false, false};
-    if (!configured[ENC]) {
-        cudaError_t e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(nrc_train_step_kernel<ENC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kTotal);
-        if (e != cudaSuccess) return e;
-        configured[ENC] = true;
-    }
     // Cooperative launch: the grid barrier needs every CTA resident (<= 128 CTAs, one per SM).
     void* args[2] = {const_cast<TrainArgs*>(&a), const_cast<GridMeta*>(&gm)};
-    const bool multi = a.apply && a.dp_world <= 1 && a.n_steps > 1;
+    const bool multi = a.apply && a.n_steps > 1;
     const void* fn = multi ? reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, true>)
                            : reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, false>);
     return cudaLaunchCooperativeKernel(fn, dim3(train_grid(a.n_local)), dim3(kTrainThreads), args, L::kTotal, stream);

@@ -175,9 +175,9 @@ __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, int a_mn_maj
            | ((uint32_t)(N >> 3) << 17)
            | ((uint32_t)(M >> 4) << 24);
 }
-// Same with an fp16 accumulator: D is stored as packed half2, two N elements per 32-bit TMEM column (the layout of a
-// TMEM A operand), rounded to fp16 after every K=16 instruction -- the arithmetic of the reference's
-// wmma::accumulator<__half> fragments (tcnn fully_fused_mlp.cu:68).
+// Same with an fp16 accumulator: D keeps ONE fp16 per 32-bit TMEM column (low half; tools/umma_probe.cu ts_f16acc), rounded
+// to fp16 after every K=16 instruction -- the arithmetic of the reference's wmma::accumulator<__half> fragments
+// (tcnn fully_fused_mlp.cu:68).
 __host__ __device__ constexpr uint32_t umma_idesc_f16_acc16(int M, int N, int a_mn_major, int b_mn_major) {
     return umma_idesc_f16(M, N, a_mn_major, b_mn_major) & ~(3u << 4);
 }
@@ -227,6 +227,12 @@ __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_
 __device__ __forceinline__ uint32_t pack_relu_h2(float a, float b) {
     uint32_t r;
     asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
+// relu on a packed half2 word (max.f16x2 with zero: HMNMX2)
+__device__ __forceinline__ uint32_t relu_h2(uint32_t v) {
+    uint32_t r;
+    asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(0u));
     return r;
 }
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
