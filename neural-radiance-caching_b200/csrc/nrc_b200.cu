@@ -213,8 +213,8 @@ static int build_model(Net* n) {
     CU(cudaMalloc(&n->steps, P * 4)); CU(cudaMalloc(&n->grad_f32, P * 4));
     CU(cudaMalloc(&n->params_img, (size_t)n->n_mlp * 2));
     CU(cudaMalloc(&n->ema_img, (size_t)n->n_mlp * 2));
-    CU(cudaMalloc(&n->barrier_counter, 4));
-    CU(cudaMemset(n->barrier_counter, 0, 4));
+    CU(cudaMalloc(&n->barrier_counter, kBarrierWords * 4));
+    CU(cudaMemset(n->barrier_counter, 0, kBarrierWords * 4));
     n->barrier_total = 0;
     CU(cudaMalloc(&n->partials, (size_t)kMaxTrainTiles * n->n_mlp * 4));
     CU(cudaMalloc(&n->loss_partials, kMaxTrainTiles * 4));
@@ -463,7 +463,7 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.partials = h->partials; a.grid_grad = h->grid_grad; a.loss_partials = h->loss_partials;
     a.grad_f32 = h->grad_f32; a.loss_out = h->loss_d;
     a.barrier_counter = h->barrier_counter;
-    a.barrier_target = h->barrier_total + train_grid(n_local);   // value of the counter once every CTA reached the FIRST barrier
+    a.barrier_target = h->barrier_total + train_barrier_arrivals(n_local);   // top counter once every CTA reached the FIRST barrier
     a.n_params = h->n_params; a.n_mlp = h->n_mlp;
     a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
     a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
@@ -492,7 +492,7 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
 static int launch_and_commit(Net* h, const TrainArgs& a, uint32_t n_barriers) {
     CU(launch_train_step(h->encoding, a, h->gm, h->stream));
     h->launches += 1;
-    h->barrier_total += n_barriers * train_grid(a.n_local);
+    h->barrier_total += n_barriers * train_barrier_arrivals(a.n_local);
     if (a.apply) {
         h->step += a.n_steps;
         if (a.dp_world > 1) h->dp_seq += a.n_steps;

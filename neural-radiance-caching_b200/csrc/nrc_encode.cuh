@@ -301,6 +301,127 @@ __device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t si
     return *reinterpret_cast<uint32_t*>(&acc);
 }
 
+// ---- Pipelined gather for the query kernel ------------------------------------------------------------------------------
+// The query kernel's hash encode is bound by the L1TEX wavefront rate: on the fine levels every lane of a warp touches its
+// own 128-byte line, so each of the 8 corner loads costs ~32 wavefronts.  Two changes cut that cost without touching the
+// arithmetic (weights, fp16 FMA chain in corner order c = dx + 2 dy + 4 dz, exactly as grid_level above):
+//  * x-neighbours share an aligned 8-byte pair whenever the first corner's entry index is even in x: the hash multiplies x by
+//    the prime 1, so for even x  idx(x+1) = idx(x) ^ 1  (hashed levels), and on dense levels idx(x+1) = idx(x) + 1.  One 64-bit
+//    load then fetches both corners; only lanes with an odd first index issue a separate (predicated) load for the second
+//    corner: 4 + ~2 instead of 8 wavefront groups per level.
+//  * issue / consume are split so that the loads of level l+1 are in flight while the FMA chain of level l runs
+//    (GridFetch holds what is pending: 12 words + 3 fractions + flags).
+// floor() goes through the round-down magic add (p + 1.5*2^23 rounded toward -inf holds floor(p) in its low mantissa bits;
+// exact for |p| < 2^22, i.e. |x| < 8 at the finest level), so no XU-pipe instruction (FRND / F2I) is left.
+#ifndef NRC_HASH_PAIR
+#define NRC_HASH_PAIR 1          // 0: eight 4-byte loads per level (A/B builds); 1: aligned 8-byte pairs along x
+#endif
+struct GridFetch {
+    float f[3];                 // position inside the cell
+#if NRC_HASH_PAIR
+    uint32_t pa[4], pb[4];      // low / high word of the aligned pair that holds corner (0, dy, dz)
+    uint32_t c1[4];             // corner (1, dy, dz) where it is not the pair's other word (lanes with sep set)
+    uint32_t lo;                // bit j: index of corner (0, dy, dz) is odd (it is the pair's HIGH word)
+    uint32_t sep;               // bit j: corner (1, dy, dz) is NOT the other word of the pair
+#else
+    uint32_t v[8];
+#endif
+};
+// SMEM: the level's table has been staged in shared memory (smem_table = its 32-bit shared address)
+template <bool SMEM>
+__device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table, uint32_t smem_table, uint32_t size_mask, uint32_t sy,
+                                           uint32_t sz, float scale, bool dense, float x, float y, float z) {
+    const float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
+    uint32_t g[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+        const float t = __fadd_rd(p[d], NRC_RINT_MAGIC);               // floor(p) + 1.5 * 2^23, exact
+        g[d] = __float_as_uint(t) - 0x4B400000u;                       // two's-complement floor(p)  (== (uint32_t)(int)floorf(p))
+        F.f[d] = p[d] - (t - NRC_RINT_MAGIC);
+    }
+    uint32_t i0[4], i1[4];
+    if (dense) {
+        const uint32_t cy[2] = {g[1] * sy, g[1] * sy + sy}, cz[2] = {g[2] * sz, g[2] * sz + sz};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t s = g[0] + cy[j & 1] + cz[j >> 1];
+            i0[j] = s & size_mask;
+            i1[j] = (s + 1) & size_mask;
+        }
+    } else {
+        const uint32_t cx[2] = {g[0] & size_mask, (g[0] + 1) & size_mask};
+        const uint32_t hy = g[1] * 2654435761u, hz = g[2] * 805459861u;
+        const uint32_t cy[2] = {hy & size_mask, (hy + 2654435761u) & size_mask};
+        const uint32_t cz[2] = {hz & size_mask, (hz + 805459861u) & size_mask};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            i0[j] = cx[0] ^ cy[j & 1] ^ cz[j >> 1];
+            i1[j] = cx[1] ^ cy[j & 1] ^ cz[j >> 1];
+        }
+    }
+#if NRC_HASH_PAIR
+    // bit 0 of the four first-corner indices: lo = sum (i0[j] & 1) << j
+    F.lo = (i0[0] & 1u) | ((i0[1] & 1u) << 1) | ((i0[2] & 1u) << 2) | ((i0[3] & 1u) << 3);
+    // hashed: the x neighbour is the other word of the pair exactly when x is even (then idx(x+1) = idx(x) ^ 1): one bit for the
+    // four pairs; dense: when the first index is even.
+    F.sep = dense ? F.lo : ((g[0] & 1u) ? 0xFu : 0u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const uint32_t need = (F.sep >> j) & 1u;
+        F.c1[j] = 0u;
+        if constexpr (SMEM) {
+            const uint32_t a0 = smem_table + (i0[j] & ~1u) * 4u, a1 = smem_table + i1[j] * 4u;
+            asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(F.pa[j]), "=r"(F.pb[j]) : "r"(a0));
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}" : "+r"(F.c1[j]) : "r"(a1), "r"(need));
+        } else {
+            asm volatile("ld.global.nc.v2.b32 {%0, %1}, [%2];" : "=r"(F.pa[j]), "=r"(F.pb[j]) : "l"(table + (i0[j] & ~1u)));
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.global.nc.b32 %0, [%1];\n\t}" : "+r"(F.c1[j]) : "l"(table + i1[j]), "r"(need));
+        }
+    }
+#else
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if constexpr (SMEM) {
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "r"(smem_table + i0[j] * 4u));
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "r"(smem_table + i1[j] * 4u));
+        } else {
+            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(table + i0[j]));
+            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(table + i1[j]));
+        }
+    }
+#endif
+}
+// The level's two features: result = fma((half)w_c, v_c, result) over the corners in the reference's order (grid.h:146-163),
+// w_c = ((1 * wx) * wy) * wz in fp32.  Two weights are converted per F2FP; the FMA reads its half through the .H0_H0 /
+// .H1_H1 operand selectors.
+__device__ __forceinline__ uint32_t grid_consume(const GridFetch& F) {
+    const float fx[2] = {1.0f - F.f[0], F.f[0]}, fy[2] = {1.0f - F.f[1], F.f[1]}, fz[2] = {1.0f - F.f[2], F.f[2]};
+    const float wxy[4] = {fx[0] * fy[0], fx[1] * fy[0], fx[0] * fy[1], fx[1] * fy[1]};
+    __half2 acc = __float2half2_rn(0.0f);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {          // j = dy + 2 dz: corners c = 2j (dx = 0) and 2j + 1 (dx = 1)
+#if NRC_HASH_PAIR
+        const bool hi = (F.lo >> j) & 1u, sep = (F.sep >> j) & 1u;
+        const uint32_t v0 = hi ? F.pb[j] : F.pa[j];
+        const uint32_t other = hi ? F.pa[j] : F.pb[j];
+        const uint32_t v1 = sep ? F.c1[j] : other;
+#else
+        const uint32_t v0 = F.v[2 * j], v1 = F.v[2 * j + 1];
+#endif
+        const uint32_t wp = pack_h2(wxy[2 * (j & 1)] * fz[j >> 1], wxy[2 * (j & 1) + 1] * fz[j >> 1]);
+        const __half2 w2 = *reinterpret_cast<const __half2*>(&wp);
+        acc = __hfma2(__low2half2(w2), *reinterpret_cast<const __half2*>(&v0), acc);
+        acc = __hfma2(__high2half2(w2), *reinterpret_cast<const __half2*>(&v1), acc);
+    }
+    return *reinterpret_cast<uint32_t*>(&acc);
+}
+template <int L, bool SMEM0>
+__device__ __forceinline__ void grid_issue_level(GridFetch& F, const float (&q)[15], const __half2* grid, uint32_t smem_level0, const GridMeta& gm) {
+    const uint32_t size = gm.offset[L + 1] - gm.offset[L];
+    grid_issue<(L == 0 && SMEM0)>(F, grid + gm.offset[L], smem_level0, size - 1, gm.stride_y[L], gm.stride_z[L], gm.scale[L],
+                                  (gm.dense_mask >> L) & 1, q[0], q[1], q[2]);
+}
+
 // Levels [L0, L1) -> e[L0 .. L1), the level index a compile-time constant.
 template <bool NC, int L0, int L1, int N>
 __device__ __forceinline__ void grid_levels(const float (&q)[15], const __half2* grid, const GridMeta& gm, uint32_t (&e)[N]) {

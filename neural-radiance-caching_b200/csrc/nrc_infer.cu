@@ -25,6 +25,12 @@
 
 namespace nrcb {
 
+#ifndef NRC_HASH_GATHER
+#define NRC_HASH_GATHER 1         // 0: level after level with 8 loads each (round-1 form, A/B builds); 1: pipelined gather (nrc_encode.cuh)
+#endif
+#ifndef NRC_HASH_SMEM0
+#define NRC_HASH_SMEM0 1          // grid level 0 staged in shared memory
+#endif
 #ifndef NRC_INFER_PIPELINE
 #define NRC_INFER_PIPELINE 1      // 0: encode, then the six layers, tile after tile (A/B builds; the Hash kernel always runs that loop)
 #endif
@@ -45,7 +51,12 @@ struct InferSmem {
     // Frequency only (E = 80): encoded tile = K-major A image of the input layer, per group.  Hash features (E = 64) fit
     // the 32 operand columns in TMEM, and its gathers want the shared-memory carve-out small (L1 capacity).
     static constexpr int kA0 = E > 64 ? kTile * E * 2 : 0;
-    static constexpr int kA0Off = kWeights;
+    // Hash only: level 0 of the grid (16^3 = 4096 entries x 2 fp16 = 16 KB, grid.h:692-723) staged in shared memory for the whole
+    // kernel: its lookups are the least coherent per byte of table (every query of an incoherent batch hits it) and an LDS costs
+    // ~1/8 of the L1TEX wavefronts of a divergent LDG.  The finer levels (128 KB each and up) stay in L1 / L2.
+    static constexpr int kL0 = (E > 64 || !NRC_HASH_SMEM0 || !NRC_HASH_GATHER) ? 0 : 4096 * 4;
+    static constexpr int kL0Off = kWeights;
+    static constexpr int kA0Off = kL0Off + kL0;
     static constexpr int kInOff = kA0Off + kGroups * kA0;
     static constexpr int kOutOff = kInOff + kGroups * kStage;
     static constexpr int kAcc = kTile * 12 + kTile * 16;   // fused accumulation: throughput (1536 B) + output (2048 B) of a tile
@@ -88,6 +99,35 @@ __device__ __forceinline__ void issue_layer(uint32_t sbase, uint32_t a0, uint32_
     umma_commit(d_ready);
 }
 
+// Hash encode of one query straight into the TMEM A operand (32 words = 64 fp16 features at columns tA .. tA+31): the 16 grid
+// levels are software-pipelined (level l+1's loads in flight during level l's FMA chain, nrc_encode.cuh) and leave for TMEM in
+// chunks of 8 words, so at most 8 result words + two levels of pending loads are live.
+template <int L>
+__device__ __forceinline__ void hash_levels_pipelined(GridFetch (&F)[2], uint32_t (&w)[8], const float (&q)[15], const __half2* grid,
+                                                      uint32_t smem_l0, const GridMeta& gm, uint32_t tA) {
+    if constexpr (L < 16) {
+        if constexpr (L + 1 < 16) grid_issue_level<L + 1, NRC_HASH_SMEM0 != 0>(F[(L + 1) & 1], q, grid, smem_l0, gm);
+        w[L & 7] = grid_consume(F[L & 1]);
+        if constexpr ((L & 7) == 7) tmem_st8(tA + (L >> 3) * 8, w);
+        hash_levels_pipelined<L + 1>(F, w, q, grid, smem_l0, gm, tA);
+    }
+}
+__device__ __forceinline__ void encode_hash_to_tmem(const float (&q)[15], const __half2* grid, uint32_t smem_l0, const GridMeta& gm, uint32_t tA) {
+    GridFetch F[2];
+    uint32_t w[8];
+    grid_issue_level<0, NRC_HASH_SMEM0 != 0>(F[0], q, grid, smem_l0, gm);
+    hash_levels_pipelined<0>(F, w, q, grid, smem_l0, gm, tA);
+    uint32_t ob[12];                                                                          // one-blob: words 16..27
+#pragma unroll
+    for (int d = 0; d < 6; d += 2) oneblob_pair<false>(q[3 + d], q[4 + d], ob + 2 * d);
+    {
+        const uint32_t v[8] = {ob[0], ob[1], ob[2], ob[3], ob[4], ob[5], ob[6], ob[7]};
+        tmem_st8(tA + 16, v);
+    }
+    const uint32_t v[8] = {ob[8], ob[9], ob[10], ob[11], pack_h2(q[9], q[10]), pack_h2(q[11], q[12]), pack_h2(q[13], q[14]), 0x3C003C00u};
+    tmem_st8(tA + 24, v);
+}
+
 // ENC: 0 = Frequency (E = 80), 1 = Hash (E = 64).  ACC16: fp16 accumulators (one fp16 per 32-bit TMEM column, rounded after
 // every K = 16 instruction: the arithmetic of the reference's wmma::accumulator<__half>, fully_fused_mlp.cu:68) instead of fp32.
 template <int ENC, bool ACC16>
@@ -117,8 +157,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         for (int g = 0; g < kGroups; ++g) { mbar_init(&in_full[g], 1); mbar_init(&d_ready[g], 1); mbar_init(&acc_full[g], 1); }
         mbar_init(w_full, 1);
         fence_mbar_init();
-        mbar_arrive_expect_tx(w_full, L::kWeights);
+        mbar_arrive_expect_tx(w_full, L::kWeights + L::kL0);
         bulk_g2s(smem, w_img, L::kWeights, w_full);
+        if constexpr (L::kL0 != 0) bulk_g2s(smem + L::kL0Off, params + (64 * E + 4 * 4096 + 16 * 64), L::kL0, w_full);   // grid level 0
     }
     if (warp == 0) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
@@ -331,7 +372,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         } else {
         uint32_t par = 0;
         if (t < n_tiles) load_tile(t, 0);
-        if ((warp & 3) == 0) mbar_wait(w_full, 0);       // issuing warp: the weight image has landed
+        if (ENC == 1 || (warp & 3) == 0) mbar_wait(w_full, 0);   // weight image (issuing warp) and staged grid level 0 (every gathering thread) have landed
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
             float q[15];
@@ -342,7 +383,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             if (t + tile_stride < n_tiles) load_tile(t + tile_stride, par ^ 1);
 
             // ---- encode -> A operand of the input layer (its previous contents were consumed long ago)
-            {
+            if constexpr (ENC == 1 && NRC_HASH_GATHER != 0) {
+                encode_hash_to_tmem(q, grid, smem_u32(smem + L::kL0Off), gm, tA);
+            } else {
                 uint32_t e[E / 2];
                 if constexpr (ENC == 0) encode_frequency(q, e);
                 else encode_hash(q, grid, gm, e);

@@ -44,8 +44,8 @@ struct TrainArgs {
     float* loss_partials;            // [n_tiles]
     float* grad_f32;                 // [n_params] reduced fp32 gradient (apply = 0: the all-reduce payload)
     float* loss_out;
-    uint32_t* barrier_counter;       // monotonically increasing arrival counter
-    uint32_t barrier_target;         // value the counter reaches when every CTA has arrived at the launch's FIRST barrier
+    uint32_t* barrier_counter;       // monotonically increasing arrival counters: [0] top (polled), [32 * (1 + g)] group g
+    uint32_t barrier_target;         // value the top counter reaches when every CTA has arrived at the launch's FIRST barrier
     uint32_t n_params, n_mlp;
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
     float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
@@ -76,7 +76,17 @@ struct TrainArgs {
 constexpr int kMaxDpRanks = 8;
 // CTAs of a step launch: one per 128-sample tile, but never fewer than 128 -- short data-parallel shards keep the gradient
 // reduction / optimizer phase 128 slices wide (the extra CTAs skip phase 1).  The grid barrier counts this many arrivals.
-inline uint32_t train_grid(uint32_t n_local) { const uint32_t t = n_local / 128; return t < 128 ? 128 : t; }
+inline __host__ __device__ uint32_t train_grid(uint32_t n_local) { const uint32_t t = n_local / 128; return t < 128 ? 128 : t; }
+// Two-level grid barrier (nrc_train.cu grid_arrive): CTAs arrive in groups of kBarrierFan on per-group counters, the last
+// arriver of a group on the top counter; one barrier instance adds this many arrivals to the top counter.
+#ifndef NRCB_BARRIER_TREE
+#define NRCB_BARRIER_TREE 1
+#endif
+constexpr uint32_t kBarrierFan = 16;
+constexpr uint32_t kBarrierWords = 32 * (1 + 16);   // top counter + up to 16 group counters, 128 bytes apart
+inline __host__ __device__ uint32_t train_barrier_arrivals(uint32_t n_local) {
+    return NRCB_BARRIER_TREE ? train_grid(n_local) / kBarrierFan : train_grid(n_local);
+}
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream);
 
 // Adam + EMA from an already reduced fp32 gradient (after a data-parallel all-reduce); clears grid_grad.

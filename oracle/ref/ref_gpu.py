@@ -30,6 +30,11 @@ def lib():
         L.nrc_ref_n_params.argtypes = [vp]
         L.nrc_ref_get_params.argtypes = [vp, i32, vp]
         L.nrc_ref_set_master.argtypes = [vp, vp]
+        if hasattr(L, "nrc_refh_accumulate"):    # the reference's frame helper kernels (ref_helpers_wrap.cu)
+            L.nrc_refh_last_error.restype = ctypes.c_char_p
+            L.nrc_refh_accumulate.argtypes = [vp, vp, vp, i32, i32, i32, i32]
+            L.nrc_refh_propagate.argtypes = [vp, vp, vp, vp, i32, i32]
+            L.nrc_refh_permute.argtypes = [vp, vp, vp, vp, vp, i32]
         _lib = L
     return _lib
 
@@ -75,3 +80,21 @@ class RefNetwork:
         m = np.ascontiguousarray(master, dtype=np.float32)
         assert m.size == self.n
         _ck(lib().nrc_ref_set_master(self.h, m.ctypes.data))
+
+
+# ---- the reference's frame helper kernels (nrc/shaders/nrc_helpers.cu:77-249), unmodified source; raw device pointers
+def _hck(rc):
+    if rc != 0:
+        raise RuntimeError("reference helpers: " + lib().nrc_refh_last_error().decode())
+
+
+def accumulate_render_radiance(radiance_d, throughput_d, output_d, width, height, mode, iteration):
+    _hck(lib().nrc_refh_accumulate(radiance_d, throughput_d, output_d, width, height, mode, iteration))
+
+
+def propagate_train_radiance(end_vertices_d, end_radiance_d, records_d, targets_d, tiles_x, tiles_y):
+    _hck(lib().nrc_refh_propagate(end_vertices_d, end_radiance_d, records_d, targets_d, tiles_x, tiles_y))
+
+
+def permute_train_data(q_src_d, q_dst_d, t_src_d, t_dst_d, permutation_d, num_records):
+    _hck(lib().nrc_refh_permute(q_src_d, q_dst_d, t_src_d, t_dst_d, permutation_d, num_records))

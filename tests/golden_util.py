@@ -54,3 +54,62 @@ def infer_queries():
 def load(name):
     p = os.path.join(GOLDEN_DIR, name)
     return np.load(p) if os.path.exists(p) else None
+
+
+# ---- NEXT rows (frame helpers): seeded inputs of tests/golden/ref_helpers.npz and ref_frame_*.npz
+HELPER_W, HELPER_H = 48, 20                   # accumulate: 960 pixels
+HELPER_TILES_X, HELPER_TILES_Y = 40, 25       # propagate: 1000 tiles
+HELPER_RECORDS = 4096
+ACC_CASES = [(0, 0), (0, 3), (2, 0), (4, 0), (5, 1), (1, 0), (3, 2)]   # (nrc::RenderMode, iterationIndex)
+PERMUTE_CASES = [65536, 1000, 70000]          # numTrainingRecords (70000: clamped to 65536, nrc_helpers.cu:237)
+
+
+def helper_inputs():
+    """Seeded inputs for the reference's accumulate / propagate / permute kernels (nrc_helpers.cu:77-249)."""
+    rng = np.random.Generator(np.random.PCG64(4711))
+    n_px = HELPER_W * HELPER_H
+    d = {"acc_radiance": rng.uniform(0, 2, (n_px, 3)).astype(np.float32),
+         "acc_throughput": rng.uniform(0, 1, (n_px, 3)).astype(np.float32),
+         "acc_output": rng.uniform(0, 1, (n_px, 4)).astype(np.float32)}
+    s = _synth()
+    n_tiles = HELPER_TILES_X * HELPER_TILES_Y
+    ev, rec, used = s.training_chains(n_tiles, n_records=HELPER_RECORDS, seed=99, max_len=5)
+    d.update(prop_ev=ev, prop_rec=rec, prop_used=used,
+             prop_end_radiance=rng.uniform(0, 3, (n_tiles, 3)).astype(np.float32),
+             prop_targets=rng.uniform(0, 1, (HELPER_RECORDS, 3)).astype(np.float32))
+    d["perm_q"] = s.cornell_queries(65536, seed=31)
+    d["perm_t"] = s.radiance_targets(d["perm_q"], seed=31)
+    d["perm"] = rng.permutation(65536).astype(np.int32)      # stands for the reference's cuRAND + CUB result (NRCUtil.cu:20-35)
+    return d
+
+
+def digest(a):
+    import hashlib
+    return np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8)
+
+
+# One small frame through the whole NRC sequence of Device::render (Device.cpp:2495-2515): 320x240 pixels, 2x2-pixel tiles
+FRAME_W, FRAME_H, FRAME_TILE = 320, 240, 2
+FRAME_SEED = 5
+
+
+def frame_inputs(enc):
+    """Seeded frame: queries (pixels + tile tails), throughput, output image, suffix end vertices, training records,
+    training queries / targets, and the permutation the reference's permute_train_data is given (this library's keyed
+    bijection, so that both sides train on identical batches)."""
+    s = _synth()
+    entry.load_package()
+    pkg = importlib.import_module("nrc_b200")
+    n_px = FRAME_W * FRAME_H
+    tx, ty = FRAME_W // FRAME_TILE, FRAME_H // FRAME_TILE
+    n_tiles = tx * ty
+    rng = np.random.Generator(np.random.PCG64(2024 + enc))
+    q = np.concatenate([s.cornell_frame(FRAME_W, FRAME_H, seed=11), s.cornell_queries(n_tiles, seed=12)])
+    ev, rec, used = s.training_chains(n_tiles, seed=13, max_len=3)
+    tq = s.cornell_queries(65536, seed=14)
+    tt = s.radiance_targets(tq, seed=14)
+    tt[used:] = 0
+    perm = np.array([pkg.permutation(i, FRAME_SEED) for i in range(65536)], dtype=np.int32)
+    return {"queries": q, "n_px": n_px, "tiles": (tx, ty), "throughput": rng.uniform(0, 1, (n_px, 3)).astype(np.float32),
+            "output": rng.uniform(0, 1, (n_px, 4)).astype(np.float32), "ev": ev, "rec": rec, "used": used,
+            "train_q": tq, "train_t": tt, "perm": perm}

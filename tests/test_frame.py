@@ -208,3 +208,108 @@ def test_gpu_update_matches_explicit_sequence(pkg, orc, synth):
     assert np.array_equal(outs[0][3], outs[1][3])
     assert abs(outs[0][2] - outs[1][2]) <= 1e-6 * abs(outs[0][2])
     assert (outs[0][0][:, :3] != 0).any()                  # frame 2 sees a trained cache (EMA no longer zero)
+
+
+# ------------------------------------------------------------------ pinned by the REFERENCE's own helper kernels
+# tests/golden/ref_helpers.npz, ref_frame_*.npz: outputs of the unmodified nrc/shaders/nrc_helpers.cu kernels (and, for the
+# frame, the reference network) run on a B200 by tools/gen_golden_ref.py; inputs are regenerated from seeds (golden_util).
+import golden_util as gu  # noqa: E402
+
+
+def _helpers():
+    g = gu.load("ref_helpers.npz")
+    if g is None:
+        pytest.skip("tests/golden/ref_helpers.npz missing (generate with tools/gen_golden_ref.py on a B200)")
+    return g, gu.helper_inputs()
+
+
+def _structured(orc, ev, rec):
+    return (np.ascontiguousarray(ev).view(orc.END_VERTEX_DTYPE).reshape(-1), np.ascontiguousarray(rec).view(orc.RECORD_DTYPE).reshape(-1))
+
+
+def test_oracle_helpers_match_reference_kernels(orc):
+    """The oracle's restatement of accumulate / propagate / permute against the reference kernels' outputs, bit for bit."""
+    g, h = _helpers()
+    for mode, it in gu.ACC_CASES:
+        assert np.array_equal(orc.accumulate(h["acc_radiance"], h["acc_throughput"], h["acc_output"], mode, it), g[f"acc_m{mode}_i{it}"]), (mode, it)
+    ev, rec = _structured(orc, h["prop_ev"], h["prop_rec"])
+    assert np.array_equal(orc.propagate(ev, h["prop_end_radiance"], rec, h["prop_targets"]), g["prop_targets"])
+    for n_rec in gu.PERMUTE_CASES:      # the gather itself, with the reference-side permutation supplied
+        src = h["perm"] % min(n_rec, 65536)
+        assert np.array_equal(gu.digest(h["perm_q"][src]), g[f"perm_{n_rec}_q_digest"])
+        assert np.array_equal(gu.digest(h["perm_t"][src]), g[f"perm_{n_rec}_t_digest"])
+        assert np.array_equal(h["perm_q"][src][::97], g[f"perm_{n_rec}_q_sample"])
+
+
+@pytest.mark.gpu
+def test_gpu_helpers_match_reference_kernels(pkg):
+    """The CUDA helper kernels, through the C ABI, against the reference kernels' outputs: bit-exact."""
+    import torch
+    g, h = _helpers()
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    n_px = gu.HELPER_W * gu.HELPER_H
+    for mode, it in gu.ACC_CASES:
+        o = dev(h["acc_output"])
+        pkg.accumulate_render_radiance(dev(h["acc_radiance"]), dev(h["acc_throughput"]), o, n_px, mode, it)
+        torch.cuda.synchronize()
+        assert np.array_equal(o.cpu().numpy(), g[f"acc_m{mode}_i{it}"]), (mode, it)
+    t = dev(h["prop_targets"])
+    pkg.propagate_train_radiance(dev(h["prop_ev"]), dev(h["prop_end_radiance"]), dev(h["prop_rec"]), t, gu.HELPER_TILES_X * gu.HELPER_TILES_Y)
+    torch.cuda.synchronize()
+    assert np.array_equal(t.cpu().numpy(), g["prop_targets"])
+    for n_rec in gu.PERMUTE_CASES:
+        qd, td = torch.zeros(65536, 15, device="cuda"), torch.zeros(65536, 3, device="cuda")
+        pkg.permute_train_data_with(dev(h["perm_q"]), dev(h["perm_t"]), qd, td, dev(h["perm"]), n_rec)
+        torch.cuda.synchronize()
+        assert np.array_equal(gu.digest(qd.cpu().numpy()), g[f"perm_{n_rec}_q_digest"])
+        assert np.array_equal(gu.digest(td.cpu().numpy()), g[f"perm_{n_rec}_t_digest"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("enc,name", [(0, "freq"), (1, "hash")])
+def test_gpu_update_matches_reference_frame(pkg, enc, name):
+    """nrc_b200_update against the REFERENCE's frame sequence (its network + its helper kernels, Device.cpp:2495-2515) on
+    the same seeded frame: radiance / accumulated image / propagated targets at the radiance tolerance, the shuffled batches
+    byte for byte (digest), the four training losses at the loss-curve tolerance (2 %)."""
+    import torch
+    g = gu.load(f"ref_frame_{name}.npz")
+    if g is None:
+        pytest.skip("tests/golden/ref_frame_*.npz missing (generate with tools/gen_golden_ref.py on a B200)")
+    f = gu.frame_inputs(enc)
+    dev = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    rel = lambda a, b, floor: float((np.abs(a - b) / np.maximum(np.abs(b), floor)).max())
+    res = {}
+    for mode in (pkg.ACC_FP32, pkg.ACC_FP16):
+        net = pkg.Network()
+        net.init(0, enc)
+        net.load_master(gu.seeded_master(enc, net.n_params()[0], True))
+        q0, t0 = gu.batch(0)
+        lr = net.getLearningRate()
+        net.setHyperParams(pkg.HyperParams(0.0))         # the fixture's warm-up: weights -> EMA, Adam moments move
+        net.train(dev(q0), dev(t0))
+        net.setHyperParams(pkg.HyperParams(lr))
+        net.set_accumulator(mode)
+        n_px, (tx, ty) = f["n_px"], f["tiles"]
+        fq, out3 = dev(f["queries"]), torch.zeros((f["queries"].shape[0], 3), device="cuda")
+        thr, out4 = dev(f["throughput"]), dev(f["output"])
+        ev, rec, tq, tt = dev(f["ev"]), dev(f["rec"]), dev(f["train_q"]), dev(f["train_t"])
+        fr = pkg.Frame(fq.data_ptr(), out3.data_ptr(), n_px, tx * ty, thr.data_ptr(), out4.data_ptr(), pkg.RENDER_FULL, 2,
+                       ev.data_ptr(), rec.data_ptr(), tq.data_ptr(), tt.data_ptr(), f["used"], gu.FRAME_SEED)
+        stat = net.update(fr, want_stat=True)
+        torch.cuda.synchronize()
+        r = {"results": rel(out3.cpu().numpy()[::7], g["results"], 0.05),
+             "output": rel(out4.cpu().numpy()[::5][:, :3], g["output"][:, :3], 0.05),
+             "targets": rel(tt.cpu().numpy()[:f["used"]][::3], g["targets"], 0.05),
+             "loss": abs(stat.loss - float(g["losses"].mean())) / float(g["losses"].mean())}
+        # the shuffled batches the training steps consumed: materialise them with the stand-alone permute and compare bytes
+        qd, td = torch.zeros(65536, 15, device="cuda"), torch.zeros(65536, 3, device="cuda")
+        pkg.permute_train_data(tq, dev(f["train_t"]), qd, td, f["used"], gu.FRAME_SEED)
+        torch.cuda.synchronize()
+        assert np.array_equal(gu.digest(qd.cpu().numpy()), g["permuted_q_digest"])
+        res[mode] = r
+        print(f"[frame {name}, acc mode {mode}] max rel (floor 0.05): radiance {r['results']:.2e}, image {r['output']:.2e}, "
+              f"propagated targets {r['targets']:.2e}; mean loss of the 4 steps off by {100 * r['loss']:.3f} %")
+        assert (out4.cpu().numpy()[:, 3] == 1.0).all()
+        assert r["results"] <= 1e-2 and r["output"] <= 1e-2 and r["targets"] <= 1e-2, r
+        assert r["loss"] <= 0.02, r
+        net.destroy()

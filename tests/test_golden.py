@@ -4,19 +4,39 @@ tools/gen_golden_ref.py; inputs and weights are regenerated from seeds (tests/go
 
 CPU tests (no marker): the oracle against the reference's numbers.
 GPU tests (@gpu): the CUDA path, through the C ABI, against the reference's numbers.
-Tolerances (BASELINE.json north_star): radiance max relative error <= 1e-2 (denominator floored at RADIANCE_FLOOR,
-see tests/test_infer_gpu.py), loss curves within 2 % on 50-step window means over 1000 steps."""
+Tolerances (BASELINE.json north_star): radiance max relative error <= 1e-2 with the denominator
+floored at STATED_FLOOR = 1e-3 -- gated on the reference's TRAINED cache (ref_curve_*.npz: its EMA weights after 1000
+steps + its radiance), which is what a renderer queries; loss curves within 2 % on 50-step window means over 1000 steps.
+The random-weight fixtures (ref_infer_*.npz; mean |radiance| 0.025 / 0.045, thousands of outputs within a few fp16 ulps of
+zero) are reported on BOTH metrics: floor RANDOM_FLOOR = 0.05 (gate 1e-2) and the true relative error on |ref| > 0.01
+(gate: the fp32-accumulate arithmetic's measured 2.7 % maximum, < 3 % of those outputs above 1e-2); the fp16-accumulator
+mode (nrc_b200_set_accumulator) reproduces the reference's own arithmetic and is gated on bit-identity."""
 import numpy as np
 import pytest
 
 import golden_util as gu
 
-REL_TOL, RADIANCE_FLOOR = 1e-2, 0.05
+REL_TOL, RADIANCE_FLOOR, STATED_FLOOR = 1e-2, 0.05, 1e-3
 ENC = [(0, "freq"), (1, "hash")]
 
 
 def _rel(a, ref):
     return np.abs(a - ref) / np.maximum(np.abs(ref), RADIANCE_FLOOR)
+
+
+def _rel_at(a, ref, floor):
+    return np.abs(a - ref) / np.maximum(np.abs(ref), floor)
+
+
+def _both_metrics(got, ref, label):
+    """(max rel err at floor 0.05, max true rel err on |ref| > 0.01, fraction of those above 1e-2, bit-identical fraction)."""
+    big = np.abs(ref) > 0.01
+    true_rel = np.abs(got - ref)[big] / np.abs(ref)[big]
+    m = (float(_rel_at(got, ref, RADIANCE_FLOOR).max()), float(true_rel.max()), float(np.mean(true_rel > REL_TOL)),
+         float(np.mean(got == ref)), float(_rel_at(got, ref, STATED_FLOOR).max()))
+    print(f"[{label}] max rel err: floor 0.05 -> {m[0]:.2e}; true on |ref|>0.01 -> {m[1]:.2e} ({100 * m[2]:.2f} % > 1e-2); "
+          f"floor 1e-3 -> {m[4]:.2e}; bit-identical to the reference {100 * m[3]:.1f} %")
+    return m
 
 
 def _need(name):
@@ -35,10 +55,28 @@ def test_oracle_infer_matches_reference(orc, enc, name):
     assert (ref > 0).mean() > 0.3
     o32 = orc.infer(spec, w, q, acc_mode=0)       # fp32 accumulation (what the tcgen05 kernels do)
     o16 = orc.infer(spec, w, q, acc_mode=1)       # emulates the reference's fp16 wmma accumulators
-    assert _rel(o32, ref).max() <= REL_TOL
-    assert _rel(o16, ref).max() <= 0.5 * REL_TOL
+    m32, m16 = _both_metrics(o32, ref, f"oracle fp32-acc {name}"), _both_metrics(o16, ref, f"oracle fp16-acc {name}")
+    assert m32[0] <= REL_TOL and m32[1] <= 4e-2 and m32[2] <= 0.03      # random weights: both metrics (module docstring)
+    assert m16[0] <= 0.5 * REL_TOL and m16[2] <= 0.003
     assert np.mean(o16 == ref) > 0.97             # the fp16-accumulate restatement is ~bit-exact to the reference
     assert np.mean(o32 == ref) > 0.3
+
+
+@pytest.mark.parametrize("enc,name", ENC)
+def test_oracle_trained_cache_matches_reference_at_the_stated_floor(orc, enc, name):
+    """The reference's own trained cache (EMA weights after 1000 steps) queried by the oracle: the stated gate, 1e-2 at
+    floor 1e-3, on the arithmetic the tcgen05 kernels implement (fp32 accumulation)."""
+    g = _need(f"ref_curve_{name}.npz")
+    if "ema" not in g.files:
+        pytest.skip("fixture predates the stored trained parameters (regenerate with tools/gen_golden_ref.py)")
+    spec = orc.make_spec(enc)
+    q, ref = gu.infer_queries(), g["radiance"]
+    o32 = orc.infer(spec, g["ema"], q, acc_mode=0)
+    o16 = orc.infer(spec, g["ema"], q, acc_mode=1)
+    m32, m16 = _both_metrics(o32, ref, f"oracle fp32-acc, trained {name}"), _both_metrics(o16, ref, f"oracle fp16-acc, trained {name}")
+    assert np.abs(ref).mean() > 0.1
+    assert m32[4] <= REL_TOL, m32
+    assert m16[4] <= REL_TOL and m16[3] > 0.95, m16
 
 
 @pytest.mark.parametrize("enc,name", ENC)
@@ -101,10 +139,43 @@ def test_cuda_infer_matches_reference(pkg, enc, name):
     net.infer(torch.from_numpy(q).cuda(), out, q.shape[0])
     torch.cuda.synchronize()
     got = out.cpu().numpy()
+    net.set_accumulator(pkg.ACC_FP16)             # the reference's own arithmetic: fp16 accumulators
+    out16 = torch.zeros((q.shape[0], 3), device="cuda")
+    net.infer(torch.from_numpy(q).cuda(), out16, q.shape[0])
+    torch.cuda.synchronize()
+    got16 = out16.cpu().numpy()
     net.destroy()
-    assert np.isfinite(got).all()
-    assert _rel(got, ref).max() <= REL_TOL, _rel(got, ref).max()
+    assert np.isfinite(got).all() and np.isfinite(got16).all()
+    m32, m16 = _both_metrics(got, ref, f"cuda fp32-acc {name}"), _both_metrics(got16, ref, f"cuda fp16-acc {name}")
+    assert m32[0] <= REL_TOL and m32[1] <= 4e-2 and m32[2] <= 0.03, m32
     assert np.mean(got == ref) > 0.3
+    assert m16[0] <= 0.5 * REL_TOL and m16[2] <= 0.003 and m16[3] > 0.97, m16     # "reference-exact" mode
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("enc,name", ENC)
+def test_cuda_trained_cache_matches_reference_at_the_stated_floor(pkg, enc, name):
+    """North-star gate as BASELINE.md section 3 states it: max relative error <= 1e-2 on radiance, floor 1e-3, on the
+    reference's TRAINED weights against the reference's radiance -- default (fp32-accumulate) kernel and fp16 mode."""
+    import torch
+    g = _need(f"ref_curve_{name}.npz")
+    if "ema" not in g.files:
+        pytest.skip("fixture predates the stored trained parameters (regenerate with tools/gen_golden_ref.py)")
+    net = pkg.Network()
+    net.init(0, enc)
+    net.set_params(pkg.PARAMS_EMA_F16, g["ema"])
+    q, ref = gu.infer_queries(), g["radiance"]
+    q_d = torch.from_numpy(q).cuda()
+    res = {}
+    for mode, label in ((pkg.ACC_FP32, "fp32"), (pkg.ACC_FP16, "fp16")):
+        net.set_accumulator(mode)
+        out = torch.zeros((q.shape[0], 3), device="cuda")
+        net.infer(q_d, out, q.shape[0])
+        torch.cuda.synchronize()
+        res[label] = _both_metrics(out.cpu().numpy(), ref, f"cuda {label}-acc, trained {name}")
+    net.destroy()
+    assert res["fp32"][4] <= REL_TOL, res["fp32"]
+    assert res["fp16"][4] <= REL_TOL and res["fp16"][3] > 0.95, res["fp16"]
 
 
 @pytest.mark.gpu
@@ -156,10 +227,18 @@ def test_cuda_loss_curve_1000_steps_matches_reference(pkg, enc, name):
         # 0.2 .. 7.4 % / 0.2 .. 9.3 % from the reference's first run there, and up to 6 % from each other.
         # Gates: window 0 (still deterministic) at the north star's 2 %; windows 1-2 within 3x the largest early
         # deviation of the reference from itself (one rerun is a single draw of that spread, hence the factor);
-        rr = g["losses_rerun"].reshape(-1, 50).mean(1)
-        self_dev = np.abs(rr / rw - 1)
         assert dev[0] <= 0.02, dev[0]
-        assert np.all(dev[1:3] <= max(0.02, 3 * float(self_dev[:3].max()))), (dev[:3], self_dev[:3])
+        if "losses_runs" in g.files:
+            # the reference's own distribution: >= 10 runs of the same binary on the same inputs.  Gate: every early window
+            # (0..2) of ours inside the envelope [min, max] of the reference's runs widened by the north star's 2 %.
+            runs = g["losses_runs"].reshape(g["losses_runs"].shape[0], -1, 50).mean(2)
+            lo, hi = runs.min(0), runs.max(0)
+            print(f"[hash] windows 0..2: ours {gw[:3]}, reference envelope over {runs.shape[0]} runs {lo[:3]} .. {hi[:3]}")
+            assert np.all(gw[:3] >= lo[:3] * 0.98) and np.all(gw[:3] <= hi[:3] * 1.02), (gw[:3], lo[:3], hi[:3])
+        else:
+            rr = g["losses_rerun"].reshape(-1, 50).mean(1)
+            self_dev = np.abs(rr / rw - 1)
+            assert np.all(dev[1:3] <= max(0.02, 3 * float(self_dev[:3].max()))), (dev[:3], self_dev[:3])
         # tail (steps 150..1000): geometric-mean loss within 10 % (measured: ours 1.6 .. 6.7 %, reference rerun 1.3 %),
         # and the per-window MEDIAN losses (robust against the spikes: window MEANS of two runs of one implementation are
         # 0.14 .. 0.64 apart in rms log-ratio) no more scattered around the reference than 2x its own rerun is

@@ -65,6 +65,18 @@ def child():
             torch.cuda.synchronize()
             best.append(a.elapsed_time(b) / 20)
         res[f"enc{enc}_infer_us"] = min(best) * 1e3
+        # incoherent batch (independent random surface points, 2^21 queries = 126 MB > L2 share): the worst case for the gathers
+        qr = torch.from_numpy(np.concatenate([synth.cornell_queries(1 << 20, seed=s_) for s_ in (1, 2)])).cuda()
+        for _ in range(3):
+            net.infer(qr, out_d, 1 << 21)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(10):
+            net.infer(qr, out_d, 1 << 21)
+        b.record()
+        torch.cuda.synchronize()
+        res[f"enc{enc}_infer_random_2M_us"] = a.elapsed_time(b) / 10 * 1e3
+        del qr
         for _ in range(3):
             net.train_batches(tq_d.data_ptr(), tt_d.data_ptr(), 4)
         torch.cuda.synchronize()
