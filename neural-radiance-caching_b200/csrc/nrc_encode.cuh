@@ -302,19 +302,21 @@ __device__ __forceinline__ uint32_t grid_level(const __half2* table, uint32_t si
 }
 
 // ---- Pipelined gather for the query kernel ------------------------------------------------------------------------------
-// The query kernel's hash encode is bound by the L1TEX wavefront rate: on the fine levels every lane of a warp touches its
-// own 128-byte line, so each of the 8 corner loads costs ~32 wavefronts.  Two changes cut that cost without touching the
-// arithmetic (weights, fp16 FMA chain in corner order c = dx + 2 dy + 4 dz, exactly as grid_level above):
-//  * x-neighbours share an aligned 8-byte pair whenever the first corner's entry index is even in x: the hash multiplies x by
-//    the prime 1, so for even x  idx(x+1) = idx(x) ^ 1  (hashed levels), and on dense levels idx(x+1) = idx(x) + 1.  One 64-bit
-//    load then fetches both corners; only lanes with an odd first index issue a separate (predicated) load for the second
-//    corner: 4 + ~2 instead of 8 wavefront groups per level.
+// Same arithmetic as grid_level above (weights in fp32, fp16 FMA chain in corner order c = dx + 2 dy + 4 dz), restructured:
 //  * issue / consume are split so that the loads of level l+1 are in flight while the FMA chain of level l runs
-//    (GridFetch holds what is pending: 12 words + 3 fractions + flags).
-// floor() goes through the round-down magic add (p + 1.5*2^23 rounded toward -inf holds floor(p) in its low mantissa bits;
-// exact for |p| < 2^22, i.e. |x| < 8 at the finest level), so no XU-pipe instruction (FRND / F2I) is left.
+//    (GridFetch holds what is pending);
+//  * floor() goes through the round-DOWN magic add: t = p + 1.5*2^23 rounded toward -inf holds floor(p) in its low mantissa
+//    bits (exact for |p| < 2^22, i.e. |x| < 8 at the finest level) -- no XU-pipe instruction (FRND / F2I) is left.  The
+//    constant 0x4B400000 the bit pattern carries is never subtracted per axis: its low 22 bits are zero, so it vanishes
+//    under the table mask (tables <= 2^22 entries) and folds into the addend of the per-axis multiply otherwise;
+//  * one IMAD.WIDE per address (the table base is kept in a vector register pair on purpose: with a uniform base ptxas
+//    emits LEA + LEA.HI.X, two issue slots per gather), two weights per F2FP (the FMA selects its half with .H0_H0 / .H1_H1).
+// Measured alternatives, kept as A/B builds (profiles/r02_ab_variants.json, ncu: profiles/r02_infer_hash_*): NRC_HASH_PAIR=1
+// fetches x-neighbours as one aligned 8-byte pair where the first corner's index is even (-25 % L1 sectors, but +25 %
+// instructions for the selects: slower on the pixel-ordered frame, faster on incoherent batches); NRC_HASH_SMEM0=1 stages
+// level 0 (16 KB) in shared memory (costs L1 capacity the fine levels need: slower on both).
 #ifndef NRC_HASH_PAIR
-#define NRC_HASH_PAIR 1          // 0: eight 4-byte loads per level (A/B builds); 1: aligned 8-byte pairs along x
+#define NRC_HASH_PAIR 0
 #endif
 struct GridFetch {
     float f[3];                 // position inside the cell
@@ -327,30 +329,42 @@ struct GridFetch {
     uint32_t v[8];
 #endif
 };
+__device__ __forceinline__ uint64_t entry_addr(uint64_t table, uint32_t idx) {     // table + 4 * idx: one IMAD.WIDE.U32
+    uint64_t a;
+    asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(a) : "r"(idx), "l"(table));
+    return a;
+}
 // SMEM: the level's table has been staged in shared memory (smem_table = its 32-bit shared address)
 template <bool SMEM>
-__device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table, uint32_t smem_table, uint32_t size_mask, uint32_t sy,
+__device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table_ptr, uint32_t smem_table, uint32_t size_mask, uint32_t sy,
                                            uint32_t sz, float scale, bool dense, float x, float y, float z) {
+    constexpr uint32_t kMagicBits = 0x4B400000u;                       // bit pattern of 1.5 * 2^23
     const float p[3] = {fmaf(scale, x, 0.5f), fmaf(scale, y, 0.5f), fmaf(scale, z, 0.5f)};
-    uint32_t g[3];
+    uint32_t tb[3];                                                    // kMagicBits + floor(p) (two's complement in the low bits)
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
         const float t = __fadd_rd(p[d], NRC_RINT_MAGIC);               // floor(p) + 1.5 * 2^23, exact
-        g[d] = __float_as_uint(t) - 0x4B400000u;                       // two's-complement floor(p)  (== (uint32_t)(int)floorf(p))
+        tb[d] = __float_as_uint(t);
         F.f[d] = p[d] - (t - NRC_RINT_MAGIC);
     }
+    uint64_t table = reinterpret_cast<uint64_t>(table_ptr);
+    asm volatile("" : "+l"(table));                                    // keep the base in vector registers (see above)
     uint32_t i0[4], i1[4];
     if (dense) {
-        const uint32_t cy[2] = {g[1] * sy, g[1] * sy + sy}, cz[2] = {g[2] * sz, g[2] * sz + sz};
+        // (g0 + g1*sy + g2*sz) with g = tb - kMagicBits: the three constants collapse into one addend
+        const uint32_t base = tb[0] + tb[1] * sy + tb[2] * sz - kMagicBits * (1u + sy + sz);
+        const uint32_t cyz[4] = {base, base + sy, base + sz, base + sy + sz};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-            const uint32_t s = g[0] + cy[j & 1] + cz[j >> 1];
-            i0[j] = s & size_mask;
-            i1[j] = (s + 1) & size_mask;
+            i0[j] = cyz[j] & size_mask;
+            i1[j] = (cyz[j] + 1) & size_mask;
         }
     } else {
-        const uint32_t cx[2] = {g[0] & size_mask, (g[0] + 1) & size_mask};
-        const uint32_t hy = g[1] * 2654435761u, hz = g[2] * 805459861u;
+        // masked per-axis terms (& distributes over ^).  x: prime 1; the magic constant's low 22 bits are zero, so it drops
+        // out under masks below 2^22 and is subtracted only for larger tables.  y, z: folded into the multiply's addend.
+        const uint32_t g0 = size_mask < (1u << 22) ? tb[0] : tb[0] - kMagicBits;
+        const uint32_t cx[2] = {g0 & size_mask, (g0 + 1) & size_mask};
+        const uint32_t hy = tb[1] * 2654435761u - kMagicBits * 2654435761u, hz = tb[2] * 805459861u - kMagicBits * 805459861u;
         const uint32_t cy[2] = {hy & size_mask, (hy + 2654435761u) & size_mask};
         const uint32_t cz[2] = {hz & size_mask, (hz + 805459861u) & size_mask};
 #pragma unroll
@@ -364,7 +378,7 @@ __device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table, u
     F.lo = (i0[0] & 1u) | ((i0[1] & 1u) << 1) | ((i0[2] & 1u) << 2) | ((i0[3] & 1u) << 3);
     // hashed: the x neighbour is the other word of the pair exactly when x is even (then idx(x+1) = idx(x) ^ 1): one bit for the
     // four pairs; dense: when the first index is even.
-    F.sep = dense ? F.lo : ((g[0] & 1u) ? 0xFu : 0u);
+    F.sep = dense ? F.lo : ((tb[0] & 1u) ? 0xFu : 0u);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const uint32_t need = (F.sep >> j) & 1u;
@@ -374,8 +388,8 @@ __device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table, u
             asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(F.pa[j]), "=r"(F.pb[j]) : "r"(a0));
             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.shared.b32 %0, [%1];\n\t}" : "+r"(F.c1[j]) : "r"(a1), "r"(need));
         } else {
-            asm volatile("ld.global.nc.v2.b32 {%0, %1}, [%2];" : "=r"(F.pa[j]), "=r"(F.pb[j]) : "l"(table + (i0[j] & ~1u)));
-            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.global.nc.b32 %0, [%1];\n\t}" : "+r"(F.c1[j]) : "l"(table + i1[j]), "r"(need));
+            asm volatile("ld.global.nc.v2.b32 {%0, %1}, [%2];" : "=r"(F.pa[j]), "=r"(F.pb[j]) : "l"(entry_addr(table, i0[j] & ~1u)));
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\t@p ld.global.nc.b32 %0, [%1];\n\t}" : "+r"(F.c1[j]) : "l"(entry_addr(table, i1[j])), "r"(need));
         }
     }
 #else
@@ -385,8 +399,8 @@ __device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table, u
             asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "r"(smem_table + i0[j] * 4u));
             asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "r"(smem_table + i1[j] * 4u));
         } else {
-            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(table + i0[j]));
-            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(table + i1[j]));
+            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(entry_addr(table, i0[j])));
+            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(entry_addr(table, i1[j])));
         }
     }
 #endif

@@ -29,7 +29,7 @@ namespace nrcb {
 #define NRC_HASH_GATHER 1         // 0: level after level with 8 loads each (round-1 form, A/B builds); 1: pipelined gather (nrc_encode.cuh)
 #endif
 #ifndef NRC_HASH_SMEM0
-#define NRC_HASH_SMEM0 1          // grid level 0 staged in shared memory
+#define NRC_HASH_SMEM0 0          // 1: grid level 0 staged in shared memory (A/B builds: slower, it takes L1 capacity from the fine levels)
 #endif
 #ifndef NRC_INFER_PIPELINE
 #define NRC_INFER_PIPELINE 1      // 0: encode, then the six layers, tile after tile (A/B builds; the Hash kernel always runs that loop)

@@ -50,6 +50,7 @@ struct TrainArgs {
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
     float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
     int apply;
+    int grid_grad_fp16;              // Hash: grid gradients as half products summed with half2 atomics (the reference's arithmetic)
     // n_steps optimizer steps in ONE launch (apply = 1): step s trains on samples [s*n_local, (s+1)*n_local)
     // of `in` / `targets` (fused shuffle: destination indices perm_base + s*n_local + ...), writes its loss to
     // loss_out[s]; two grid barriers per step (gradients complete / weights updated), the last one omitted.
@@ -80,7 +81,7 @@ inline __host__ __device__ uint32_t train_grid(uint32_t n_local) { const uint32_
 // Two-level grid barrier (nrc_train.cu grid_arrive): CTAs arrive in groups of kBarrierFan on per-group counters, the last
 // arriver of a group on the top counter; one barrier instance adds this many arrivals to the top counter.
 #ifndef NRCB_BARRIER_TREE
-#define NRCB_BARRIER_TREE 1
+#define NRCB_BARRIER_TREE 0      // measured: the two dependent L2 round trips cost more than the serialised arrivals (+1.3 us per barrier, profiles/r02_ab_variants.json)
 #endif
 constexpr uint32_t kBarrierFan = 16;
 constexpr uint32_t kBarrierWords = 32 * (1 + 16);   // top counter + up to 16 group counters, 128 bytes apart

@@ -165,25 +165,29 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
     if (is_matrix) a.ema_img[img_index(i, E)] = __float2half_rn(filtered);
 }
 
-// Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and two groups
-// in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
+#ifndef NRCB_ADAM_GROUPS
+#define NRCB_ADAM_GROUPS 4
+#endif
+// Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and NRCB_ADAM_GROUPS groups
+// in flight (two in round 1: 13.7 us for the 26 MB pass, latency-bound): the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
 // load_g(j) returns the reduced fp32 gradient of grid parameters j..j+3; clear: zero the scatter accumulator behind it.
-template <class LoadG>
+template <class LoadG, class ClearG>
 __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s,
-                                                LoadG load_g, bool clear) {
+                                                LoadG load_g, ClearG clear_g) {
     // The bias-corrected learning rate depends on the parameter's own step count only; almost every touched entry has
     // been touched in every step so far, so the two powf of that common count are evaluated once per thread.
     // (evaluated after the first group of loads has been issued, so it overlaps their latency)
     const uint32_t common = a.opt_step + s;
     float lr_common = 0.0f;
     bool have_lr = false;
-    for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 8 * kTrainThreads) {
-        float4 g[2], w[2], m1[2], m2[2];
-        uint4 st[2];
-        uint2 em[2], pr[2];
-        bool live[2];
+    constexpr int kG = NRCB_ADAM_GROUPS;   // float4 groups of one thread in flight: 7 vector loads each (one L2 round trip for all)
+    for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 4 * kG * kTrainThreads) {
+        float4 g[kG], w[kG], m1[kG], m2[kG];
+        uint4 st[kG];
+        uint2 em[kG], pr[kG];
+        bool live[kG];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < kG; ++u) {
             const uint32_t j = j0 + u * 4 * kTrainThreads;
             live[u] = j < ghi;
             if (live[u]) {
@@ -202,7 +206,7 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
             have_lr = true;
         }
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
+        for (int u = 0; u < kG; ++u) {
             if (!live[u]) continue;
             const uint32_t j = j0 + u * 4 * kTrainThreads, i = base + j;
             float gv[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, wv[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
@@ -241,8 +245,7 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                 *reinterpret_cast<uint4*>(a.steps + i) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
                 *reinterpret_cast<uint2*>(a.params + i) = *reinterpret_cast<uint2*>(pv);
             }
-            if (clear && (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f))   // also gradients that round to 0 in fp16
-                *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f) clear_g(j);   // also gradients that round to 0 in fp16
         }
     }
 }
@@ -560,9 +563,14 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             uint32_t v[32];
             tmem_ld32(tq + kAcc, v);
             tmem_wait_ld();
+            // a.grid_grad_fp16 (the "reference arithmetic" option, nrc_b200_set_accumulator): every contribution is the HALF product
+            // (GRAD_T)weight * grad and is added with a half2 atomic into a half2 accumulator, exactly the reference's
+            // atomicAdd(__half2) (grid.h:252-255,301-319) with its swamping of small addends; no shared-memory pre-aggregation.
+            const bool g16 = a.grid_grad_fp16 != 0;
             auto level = [&](auto LV) {
                 constexpr int lv = decltype(LV)::value;
-                constexpr bool agg = lv < kAggLevels;
+                constexpr bool agg_level = lv < kAggLevels;
+                const bool agg = agg_level && !g16;       // uniform over the CTA: the barriers below are executed by all or none
                 const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv])));
                 const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv + 1])));
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
@@ -570,7 +578,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
                 const bool active = g0 != 0.0f || g1 != 0.0f;
                 float S = 0.0f, Sinv = 0.0f;
-                if constexpr (agg) {   // common scale of this level for the whole tile
+                if (agg_level && agg) {   // common scale of this level for the whole tile
                     const uint32_t mx = __reduce_max_sync(0xffffffffu, max(__float_as_uint(fabsf(g0)), __float_as_uint(fabsf(g1))));
                     if (lane == 0 && hf == 0) atomicMax(s_max, mx);
                     workers_sync();
@@ -598,7 +606,11 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     const float wh = __half2float(__float2half_rn(wgt));   // (GRAD_T)weight, grid.h:254
                     const float v0 = wh * g0, v1 = wh * g1;
                     if (!active) continue;
-                    if constexpr (!agg) {
+                    if (g16) {
+                        const __half2 prod = __hmul2(__float2half2_rn(wgt), __floats2half2_rn(g0, g1));   // half x half, rounded to half
+                        uint32_t* gh = reinterpret_cast<uint32_t*>(a.grid_grad) + gm.offset[lv] + idx;      // half2 accumulators
+                        asm volatile("red.global.add.noftz.f16x2 [%0], %1;" ::"l"(gh), "r"(*reinterpret_cast<const uint32_t*>(&prod)) : "memory");
+                    } else if (!agg_level || !agg) {
                         asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx), "f"(v0), "f"(v1) : "memory");
                     } else {
                         // CTA-level aggregation in a shared-memory table of FIXED-POINT accumulators: 32-bit integer atomics
@@ -615,7 +627,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                         }
                     }
                 }
-                if constexpr (agg) {   // flush the table of this level: one global red per distinct entry
+                if (agg_level && agg) {   // flush the table of this level: one global red per distinct entry
                     workers_sync();
                     for (uint32_t sl = wtid; sl < kSlots; sl += 256) {
                         const uint32_t tg_ = s_tag[sl];
@@ -724,9 +736,23 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 else if (a.apply) adam_ema_param(a, lo + j, g, E, s);
             }
             if constexpr (ENC == 1) {   // grid parameters: gradient = the fp32 scatter accumulator
-                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) { return __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j)); }, true);
+                const __half* gg16 = reinterpret_cast<const __half*>(a.grid_grad);
+                auto load_g = [&](uint32_t j) {
+                    if (a.grid_grad_fp16) {      // half2 accumulators (reference arithmetic): four halves -> four floats, exact
+                        const uint2 hv = __ldcg(reinterpret_cast<const uint2*>(gg16 + j));
+                        const float2 lo2 = __half22float2(*reinterpret_cast<const __half2*>(&hv.x)), hi2 = __half22float2(*reinterpret_cast<const __half2*>(&hv.y));
+                        return make_float4(lo2.x, lo2.y, hi2.x, hi2.y);
+                    }
+                    return __ldcg(reinterpret_cast<const float4*>(a.grid_grad + j));
+                };
+                auto clear_g = [&](uint32_t j) {
+                    if (a.grid_grad_fp16) *reinterpret_cast<uint2*>(const_cast<__half*>(gg16) + j) = make_uint2(0u, 0u);
+                    else *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                };
+                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, load_g, clear_g);
                 else
-                    for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads) a.grad_f32[NMLP + j] = __ldcg(a.grid_grad + j);
+                    for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads)
+                        a.grad_f32[NMLP + j] = a.grid_grad_fp16 ? __half2float(gg16[j]) : __ldcg(a.grid_grad + j);
             }
             if (tile == 0 && warp == 0) {   // Trainer::loss (trainer.h:205-207): sum of the per-element losses
                 float l = 0.0f;
@@ -831,7 +857,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                         g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
                     }
                     return g;
-                }, false);
+                }, [](uint32_t) {});
             }
         }
     }

@@ -245,6 +245,10 @@ void nrc_oracle_infer(const nrc_oracle_spec* s, const uint16_t* params_h, const 
 }
 
 /* ---------------------------------------------------------------- training */
+/* 0: grid gradients summed in fp32 (default); 1: emulation of the reference's fp16 atomics, in sample order per thread. */
+static int g_grid_grad_mode = 0;
+void nrc_oracle_set_grid_grad_mode(int mode) { g_grid_grad_mode = mode; }
+
 typedef struct {
     nrc_oracle_state* st; const float* Wf; const float* in; const float* tgt; uint32_t lo, hi, n_norm;
     double* gw;   /* [n_mlp_params] partial weight gradients (loss-scaled)    */
@@ -336,8 +340,13 @@ static void* grad_worker(void* a) {
                     }
                     const uint32_t gi = nrc_oracle_grid_index(hashmap_size, resolution, pl[0], pl[1], pl[2]) * 2;
                     const float wh = rh(w);
-                    grid[gi] += wh * dx[level * 2];
-                    grid[gi + 1] += wh * dx[level * 2 + 1];
+                    if (g_grid_grad_mode == 0) {           /* fp32 accumulation of the exact products (what the CUDA kernels do) */
+                        grid[gi] += wh * dx[level * 2];
+                        grid[gi + 1] += wh * dx[level * 2 + 1];
+                    } else {   /* the reference's arithmetic: (GRAD_T)weight * grad in half, atomicAdd(__half2) (grid.h:252-255) */
+                        grid[gi] = rh(grid[gi] + rh(wh * dx[level * 2]));
+                        grid[gi + 1] = rh(grid[gi + 1] + rh(wh * dx[level * 2 + 1]));
+                    }
                 }
             }
         }
@@ -367,7 +376,8 @@ float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* t
     for (int i = 0; i < s->n_params; ++i) {
         double acc = 0;
         for (int t = 0; t < nthreads; ++t)
-            acc += i < s->n_mlp_params ? jobs[t].gw[i] : (double)jobs[t].gg[i - s->n_mlp_params];
+            acc = i < s->n_mlp_params ? acc + jobs[t].gw[i]
+                  : g_grid_grad_mode ? (double)rh((float)acc + jobs[t].gg[i - s->n_mlp_params]) : acc + (double)jobs[t].gg[i - s->n_mlp_params];
         grad_accum[i] += (float)acc;
     }
     for (int t = 0; t < nthreads; ++t) { loss += jobs[t].loss; free(jobs[t].gw); free(jobs[t].gg); }

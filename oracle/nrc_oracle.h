@@ -71,6 +71,9 @@ void nrc_oracle_state_set_master(nrc_oracle_state* st, const float* master, int 
  * values, trainer.h:205-207).  The gradient/loss normalisation uses n_total = 3*n_norm, with n_norm = n
  * unless the caller shards a batch (data-parallel emulation): then n_norm = global batch size and
  * `apply` = 0 only accumulates the fp32 gradient into grad_accum (n_params floats) without stepping. */
+/* Hash grid-gradient accumulation: 0 = fp32 sums of the exact products (default), 1 = the reference's arithmetic:
+ * (GRAD_T)weight * grad rounded to half, added with atomicAdd(__half2) (grid.h:252-255,301-319), emulated in sample order. */
+void nrc_oracle_set_grid_grad_mode(int mode);
 float nrc_oracle_train_step(nrc_oracle_state* st, const float* in, const float* targets, uint32_t n, int nthreads);
 float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* targets, uint32_t n, uint32_t n_norm,
                            float* grad_accum, int nthreads);

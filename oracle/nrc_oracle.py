@@ -54,6 +54,7 @@ def lib():
         L.nrc_oracle_grad_only.argtypes = [ctypes.POINTER(State), vp, vp, u32, u32, vp, i32]
         L.nrc_oracle_grad_only.restype = f32
         L.nrc_oracle_apply_grads.argtypes = [ctypes.POINTER(State), vp]
+        L.nrc_oracle_set_grid_grad_mode.argtypes = [i32]
         L.nrc_oracle_quartic_cdf.argtypes = [f32, f32]
         L.nrc_oracle_quartic_cdf.restype = f32
         L.nrc_oracle_oneblob4_aos.argtypes = [f32, ctypes.POINTER(f32 * 4)]
@@ -70,6 +71,12 @@ def lib():
         L.nrc_oracle_adjust_tile_size.argtypes = [i32, i32, i32, ctypes.POINTER(i32), ctypes.POINTER(i32)]
         _lib = L
     return _lib
+
+
+def set_grid_grad_mode(mode):
+    """0 (default): Hash grid gradients summed in fp32 (what the CUDA kernels do by default); 1: emulation of the
+    reference's arithmetic -- half products added with fp16 atomics (grid.h:252-255,301-319), in sample order."""
+    lib().nrc_oracle_set_grid_grad_mode(int(mode))
 
 
 def make_spec(encoding, log2_hashmap=15):
