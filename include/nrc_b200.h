@@ -68,10 +68,12 @@ int nrc_b200_set_learning_rate(nrc_b200_handle h, float lr);
 int nrc_b200_get_learning_rate(nrc_b200_handle h, float* lr);
 
 /* ---- additions without a reference counterpart ------------------------------------------------------ */
-/* Accumulator precision of the QUERY kernel's six matrix products.  NRC_B200_ACC_FP32 (default): fp32 accumulators in tensor
- * memory, every layer output rounded to fp16 where the reference stores fp16.  NRC_B200_ACC_FP16: fp16 accumulators, rounded
- * after every 16-wide K block -- the arithmetic of the reference's wmma::accumulator<__half> fragments (tcnn
- * fully_fused_mlp.cu:68): "reference-exact" queries at the same speed class. */
+/* Arithmetic of the matrix products.  NRC_B200_ACC_FP32 (default): fp32 accumulators in tensor memory, every layer output
+ * rounded to fp16 where the reference stores fp16; Hash grid gradients summed in fp32.  NRC_B200_ACC_FP16 = "reference
+ * arithmetic": fp16 accumulators, rounded after every 16-wide K block -- what the reference's wmma::accumulator<__half>
+ * fragments compute (tcnn fully_fused_mlp.cu:68,150-259) -- in the query kernel (measured bit-identical to the reference's
+ * radiance) and in the forward / backward chain of the training step, and Hash grid gradients as half products added with
+ * half2 atomics (grid.h:252-255,301-319).  Same speed class; the default is the more accurate arithmetic. */
 #define NRC_B200_ACC_FP32 0
 #define NRC_B200_ACC_FP16 1
 int nrc_b200_set_accumulator(nrc_b200_handle h, int mode);

@@ -474,8 +474,11 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
         a.ema_debias_new[s] = 1.0f / (1.0f - (float)pow((double)h->ema_decay, (double)(first_step + s)));
     }
     a.apply = apply;
-    // "reference arithmetic" option: besides the fp16 accumulators of the query kernel, the Hash grid gradients are scattered
-    // as half products with half2 atomics (grid.h:252-255,301-319).  The data-parallel exchange always carries fp32 sums.
+    // "reference arithmetic" option: fp16 accumulators in the query kernel AND in the forward / backward chain of the training
+    // step (fully_fused_mlp.cu:68,150-259); the Hash grid gradients are scattered as half products with half2 atomics
+    // (grid.h:252-255,301-319).  Weight gradients stay fp32 sums (the reference: fp16 split-K); the data-parallel exchange
+    // always carries fp32 sums.
+    a.acc16 = h->acc16;
     a.grid_grad_fp16 = (h->acc16 && h->encoding == NRC_B200_HASH && h->dp_world <= 1) ? 1 : 0;
     a.timeline = h->timeline;
     a.perm_n = 0; a.perm_seed = 0; a.perm_base = 0;

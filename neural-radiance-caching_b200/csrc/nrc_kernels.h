@@ -50,6 +50,7 @@ struct TrainArgs {
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
     float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
     int apply;
+    int acc16;                       // forward / backward-chain MMAs with fp16 accumulators (the reference's wmma accumulator<__half>)
     int grid_grad_fp16;              // Hash: grid gradients as half products summed with half2 atomics (the reference's arithmetic)
     // n_steps optimizer steps in ONE launch (apply = 1): step s trains on samples [s*n_local, (s+1)*n_local)
     // of `in` / `targets` (fused shuffle: destination indices perm_base + s*n_local + ...), writes its loss to

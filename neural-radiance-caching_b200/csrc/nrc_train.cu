@@ -71,15 +71,17 @@ __device__ __forceinline__ uint8_t* row_chunk(uint8_t* img, uint32_t r, uint32_t
 // K-major A [128 x K] (lbo 2048, sbo 128, +4096 per k-step); K-major B = weight image [N x K] (lbo N*16);
 // MN-major views: activation images (sbo 2048, lbo 128, +256 per k-step of 16 samples),
 //                 weight images as W^T (sbo = n_out*16, lbo 128, +256 per k-step of 16 outputs).
-__device__ __forceinline__ void mma_fwd(uint32_t d, uint32_t a_img, uint32_t w_img, int n_out, int ksteps) {
-    const uint32_t idesc = umma_idesc_f16(128, n_out, 0, 0);
+// acc16: fp16 accumulators (one fp16 per 32-bit TMEM column, rounded after every K = 16 instruction) -- the arithmetic of the
+// reference's wmma::accumulator<__half> fragments in its forward and backward kernels (fully_fused_mlp.cu:68,150-259).
+__device__ __forceinline__ void mma_fwd(uint32_t d, uint32_t a_img, uint32_t w_img, int n_out, int ksteps, bool acc16) {
+    const uint32_t idesc = acc16 ? umma_idesc_f16_acc16(128, n_out, 0, 0) : umma_idesc_f16(128, n_out, 0, 0);
 #pragma unroll
     for (int k = 0; k < 5; ++k)
         if (k < ksteps) umma_ss(d, umma_desc(a_img + k * 4096, 2048, 128), umma_desc(w_img + k * 2 * n_out * 16, n_out * 16, 128), idesc, k > 0);
 }
 // D[128 x n] = A[128 x K=n_out] * W[n_out x n]      (W image read MN-major)
-__device__ __forceinline__ void mma_dgrad(uint32_t d, uint32_t a_img, uint32_t w_img, int n_out, int n) {
-    const uint32_t idesc = umma_idesc_f16(128, n, 0, 1);
+__device__ __forceinline__ void mma_dgrad(uint32_t d, uint32_t a_img, uint32_t w_img, int n_out, int n, bool acc16) {
+    const uint32_t idesc = acc16 ? umma_idesc_f16_acc16(128, n, 0, 1) : umma_idesc_f16(128, n, 0, 1);
 #pragma unroll
     for (int k = 0; k < 4; ++k)
         if (k < n_out / 16) umma_ss(d, umma_desc(a_img + k * 4096, 2048, 128), umma_desc(w_img + k * 256, 128, n_out * 16), idesc, k > 0);
@@ -166,10 +168,10 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
 }
 
 #ifndef NRCB_ADAM_GROUPS
-#define NRCB_ADAM_GROUPS 4
+#define NRCB_ADAM_GROUPS 2      // 4 measured slower (15.4 vs 13.7 us, longer tail over the CTAs)
 #endif
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and NRCB_ADAM_GROUPS groups
-// in flight (two in round 1: 13.7 us for the 26 MB pass, latency-bound): the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
+// in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
 // load_g(j) returns the reduced fp32 gradient of grid parameters j..j+3; clear: zero the scatter accumulator behind it.
 template <class LoadG, class ClearG>
 __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s,
@@ -355,21 +357,22 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         mbar_wait(w_full, s & 1);          // weight image landed (async proxy write -> async proxy read)
         // forward
         wait_workers();
-        if (leader) { mma_fwd(acc, sX, sW, 64, E / 16); umma_commit(d_ready); }
+        const bool acc16 = a.acc16 != 0;
+        if (leader) { mma_fwd(acc, sX, sW, 64, E / 16, acc16); umma_commit(d_ready); }
         __syncwarp();
 #pragma unroll
         for (int l = 0; l < 4; ++l) {
             wait_workers();
-            if (leader) { mma_fwd(acc, sH + l * 16384, sW + L::kWin + l * 8192, 64, 4); umma_commit(d_ready); }
+            if (leader) { mma_fwd(acc, sH + l * 16384, sW + L::kWin + l * 8192, 64, 4, acc16); umma_commit(d_ready); }
             __syncwarp();
         }
         wait_workers();
-        if (leader) { mma_fwd(acc, sH + 4 * 16384, sW + L::kWin + L::kWhid, 16, 4); umma_commit(d_ready); }
+        if (leader) { mma_fwd(acc, sH + 4 * 16384, sW + L::kWin + L::kWhid, 16, 4, acc16); umma_commit(d_ready); }
         __syncwarp();
         // backward: dL/dy (G) ready
         wait_workers();
         if (leader) {
-            mma_dgrad(acc, sG, sW + L::kWin + L::kWhid, 16, 64);            // (W_out^T g)
+            mma_dgrad(acc, sG, sW + L::kWin + L::kWhid, 16, 64, acc16);     // (W_out^T g)
             umma_commit(d_ready);
             mma_wgrad(tmem_base + wg_out_col(E), sH + 4 * 16384, sG, 16);     // dW_out^T = h5^T g
         }
@@ -379,7 +382,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             wait_workers();
             if (leader) {
                 const uint32_t dl = sDl + ((3 - l) & 1) * 16384;
-                mma_dgrad(acc, dl, sW + L::kWin + l * 8192, 64, 64);
+                mma_dgrad(acc, dl, sW + L::kWin + l * 8192, 64, 64, acc16);
                 umma_commit(d_ready);
                 mma_wgrad(tmem_base + wg_hid_col(E, l), dl, sH + l * 16384, 64);  // dW_h(l+1) = delta_(l+2)^T h_(l+1)
             }
@@ -387,7 +390,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         }
         wait_workers();                   // delta_1 ready in buffer 0
         if (leader) {
-            if (ENC == 1) mma_dgrad(acc, sDl, sW, 64, 32);                      // dL/d(grid features)
+            if (ENC == 1) mma_dgrad(acc, sDl, sW, 64, 32, acc16);               // dL/d(grid features)
             mma_wgrad(tmem_base + kWgIn, sDl, sX, E);                           // dW_in = delta_1^T x
             umma_commit(d_ready);
         }
@@ -399,6 +402,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         const uint32_t tq = tmem_base + ((qd * 32u) << 16);
         const uint32_t cb = hf * 32;          // this thread's 32 accumulator columns
         const uint32_t n_total = a.n_global * 3;
+        const bool acc16 = a.acc16 != 0;     // accumulator columns hold fp16 in their low halves instead of fp32
         uint32_t ph = 0;
         auto wait_mma = [&]() { mbar_wait(d_ready, ph); ph ^= 1; tc_fence_after(); };
         auto signal = [&]() { fence_proxy_async_smem(); tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(a_ready); };
@@ -444,7 +448,8 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             tmem_wait_ld();
             uint32_t w[16];
 #pragma unroll
-            for (int i = 0; i < 16; ++i) w[i] = pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+            for (int i = 0; i < 16; ++i)
+                w[i] = acc16 ? relu_h2(__byte_perm(v[2 * i], v[2 * i + 1], 0x5410)) : pack_relu_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
 #pragma unroll
             for (int c = 0; c < 4; ++c)
                 *reinterpret_cast<uint4*>(row_chunk(smem + L::kH + l * 16384, row, hf * 4 + c)) =
@@ -461,7 +466,9 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             tmem_wait_ld();
             float y[3], gr[3];
 #pragma unroll
-            for (int c = 0; c < 3; ++c) y[c] = __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
+            for (int c = 0; c < 3; ++c)
+                y[c] = acc16 ? fmaxf(__half2float(__ushort_as_half((unsigned short)(v[c] & 0xFFFFu))), 0.0f)
+                             : __half2float(__float2half_rn(fmaxf(__uint_as_float(v[c]), 0.0f)));
             const float lum = 0.299f * y[0] + 0.587f * y[1] + 0.114f * y[2];
             const float den = lum * lum + 0.01f;
 #pragma unroll
@@ -528,7 +535,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             const __half2 zero2 = __float2half2_rn(0.0f);
 #pragma unroll
             for (int i = 0; i < 16; ++i)
-                w[i] = pack_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])) &
+                w[i] = (acc16 ? __byte_perm(v[2 * i], v[2 * i + 1], 0x5410) : pack_h2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]))) &
                        __hgt2_mask(*reinterpret_cast<const __half2*>(&hw[i]), zero2);
 #pragma unroll
             for (int c = 0; c < 4; ++c)
@@ -571,8 +578,8 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 constexpr int lv = decltype(LV)::value;
                 constexpr bool agg_level = lv < kAggLevels;
                 const bool agg = agg_level && !g16;       // uniform over the CTA: the barriers below are executed by all or none
-                const float g0 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv])));
-                const float g1 = __half2float(__float2half_rn(__uint_as_float(v[2 * lv + 1])));
+                const float g0 = acc16 ? __half2float(__ushort_as_half((unsigned short)(v[2 * lv] & 0xFFFFu))) : __half2float(__float2half_rn(__uint_as_float(v[2 * lv])));
+                const float g1 = acc16 ? __half2float(__ushort_as_half((unsigned short)(v[2 * lv + 1] & 0xFFFFu))) : __half2float(__float2half_rn(__uint_as_float(v[2 * lv + 1])));
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
                 float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;

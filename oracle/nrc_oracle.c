@@ -248,6 +248,9 @@ void nrc_oracle_infer(const nrc_oracle_spec* s, const uint16_t* params_h, const 
 /* 0: grid gradients summed in fp32 (default); 1: emulation of the reference's fp16 atomics, in sample order per thread. */
 static int g_grid_grad_mode = 0;
 void nrc_oracle_set_grid_grad_mode(int mode) { g_grid_grad_mode = mode; }
+/* accumulator emulation of the TRAINING forward pass (0 fp32, 1 fp16 per 16-wide k block like the reference's wmma fragments) */
+static int g_train_acc_mode = 0;
+void nrc_oracle_set_train_acc_mode(int mode) { g_train_acc_mode = mode; }
 
 typedef struct {
     nrc_oracle_state* st; const float* Wf; const float* in; const float* tgt; uint32_t lo, hi, n_norm;
@@ -269,7 +272,7 @@ static void* grad_worker(void* a) {
     float acts[80 + 5 * 64 + 16], g[16], d[5][64], dx[64];
     for (uint32_t i = j->lo; i < j->hi; ++i) {
         const float* q = j->in + (size_t)i * 15;
-        forward_one(s, P, j->Wf, q, acts, 0);
+        forward_one(s, P, j->Wf, q, acts, g_train_acc_mode);
         const float* x = acts;
         const float* h = acts + E; /* h[l*64 + k], l = 0..4 */
         const float* y = acts + E + 5 * 64;

@@ -74,6 +74,8 @@ void nrc_oracle_state_set_master(nrc_oracle_state* st, const float* master, int 
 /* Hash grid-gradient accumulation: 0 = fp32 sums of the exact products (default), 1 = the reference's arithmetic:
  * (GRAD_T)weight * grad rounded to half, added with atomicAdd(__half2) (grid.h:252-255,301-319), emulated in sample order. */
 void nrc_oracle_set_grid_grad_mode(int mode);
+/* Accumulators of the training forward pass: 0 = fp32 (default), 1 = fp16 per 16-wide k block (fully_fused_mlp.cu:68). */
+void nrc_oracle_set_train_acc_mode(int mode);
 float nrc_oracle_train_step(nrc_oracle_state* st, const float* in, const float* targets, uint32_t n, int nthreads);
 float nrc_oracle_grad_only(nrc_oracle_state* st, const float* in, const float* targets, uint32_t n, uint32_t n_norm,
                            float* grad_accum, int nthreads);

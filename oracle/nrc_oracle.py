@@ -55,6 +55,7 @@ def lib():
         L.nrc_oracle_grad_only.restype = f32
         L.nrc_oracle_apply_grads.argtypes = [ctypes.POINTER(State), vp]
         L.nrc_oracle_set_grid_grad_mode.argtypes = [i32]
+        L.nrc_oracle_set_train_acc_mode.argtypes = [i32]
         L.nrc_oracle_quartic_cdf.argtypes = [f32, f32]
         L.nrc_oracle_quartic_cdf.restype = f32
         L.nrc_oracle_oneblob4_aos.argtypes = [f32, ctypes.POINTER(f32 * 4)]
@@ -77,6 +78,12 @@ def set_grid_grad_mode(mode):
     """0 (default): Hash grid gradients summed in fp32 (what the CUDA kernels do by default); 1: emulation of the
     reference's arithmetic -- half products added with fp16 atomics (grid.h:252-255,301-319), in sample order."""
     lib().nrc_oracle_set_grid_grad_mode(int(mode))
+
+
+def set_train_acc_mode(mode):
+    """Accumulators of the TRAINING forward pass: 0 (default) fp32; 1 fp16 per 16-wide k block, the arithmetic of the
+    reference's wmma::accumulator<__half> fragments (fully_fused_mlp.cu:68)."""
+    lib().nrc_oracle_set_train_acc_mode(int(mode))
 
 
 def make_spec(encoding, log2_hashmap=15):
