@@ -320,23 +320,10 @@ def load_traffic():
     return {}
 
 
-def measure_l2_peak(torch):
-    """Measured L2 bandwidth of this GPU: device-to-device copy of a 24 MiB buffer (source + destination stay resident in
-    the 126 MB L2), read + write bytes, best of 20 -- the denominator of the hash-grid gather roofline."""
-    a = torch.empty(24 << 20, dtype=torch.uint8, device="cuda")
-    b = torch.empty_like(a)
-    for _ in range(5):
-        b.copy_(a)
-    best = 1e9
-    for _ in range(20):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(10):
-            b.copy_(a)
-        e1.record()
-        torch.cuda.synchronize()
-        best = min(best, e0.elapsed_time(e1) / 10)
-    return 2 * a.numel() / (best * 1e-3) / 1e9
+def measure_l2_peak(pkg):
+    """Measured L2 read bandwidth of this GPU: the library's probe kernel (16-byte L1-bypassing loads over a 32 MiB buffer that
+    stays resident in the 126 MB L2, best of 5 x 20 passes) -- the denominator of the hash-grid gather roofline."""
+    return float(pkg.l2_read_bandwidth(32 << 20, 20))
 
 
 def tensor_roofline(kernel, cfg, flop, us, peaks, traffic=None, extra=None):
@@ -518,7 +505,7 @@ def rooflines_for(enc, nq, t_inf_ms, t_tr_ms, peaks, traffic, l2_peak):
         t = traffic.get(key + "_l2")
         rl.append({"kernel": "nrc_infer_kernel<1> (hash-grid gathers)", "config": f"{nq} queries, Hash", "bound": "l2", "achieved": ach,
                    "peak": l2_peak, "unit": "GB/s", "frac": ach / l2_peak,
-                   "peak_source": "L2-resident 24 MiB device copy measured in this run (read + write)",
+                   "peak_source": "L2-resident 32 MiB read probe measured in this run (nrc_b200_debug_l2_read_bandwidth)",
                    "us_per_launch": t_inf_ms * 1e3, "traffic": t["bytes"] if t else None, "traffic_source": t["source"] if t else None})
     n_tr = NUM_BATCHES * BATCH_SIZE
     rl.append(tensor_roofline(f"nrc_train_step_kernel<{enc}>", f"{NUM_BATCHES} x {BATCH_SIZE} samples (BASELINE configs[1]), {ENC_NAME[enc]}",
@@ -563,7 +550,7 @@ def run_ours(args, enc):
     e2e = dict({"value": total_units / e2e_s, "unit": UNIT}, **e2e)
     if numa:
         e2e["numa"] = numa
-    l2_peak = measure_l2_peak(torch) if rank == 0 else 1.0
+    l2_peak = measure_l2_peak(pkg) if rank == 0 else 1.0
     rl = rooflines_for(enc, nq, t_inf, t_tr, peaks, traffic, l2_peak)
     roofline = dict(rl[0], share_of_step=t_inf / ms_step)
 

@@ -193,6 +193,10 @@ int nrc_b200_load_master(nrc_b200_handle h, const float* master_host);
 /* Debug aid: per-tile clock64 phase stamps of the training step kernel ([128][8] int64; see csrc/nrc_b200.cu). */
 int nrc_b200_debug_train_timeline(nrc_b200_handle h, int enable, long long* dst_host);
 
+/* Measurement aid: GB/s the SMs read from an L2-resident buffer of `bytes` (16-byte L1-bypassing loads, best of 5 x `reps`
+ * passes) on the current device -- the measured denominator of the hash-grid gather roofline in bench.py. */
+int nrc_b200_debug_l2_read_bandwidth(uint64_t bytes, int reps, float* gbs);
+
 const char* nrc_b200_last_error(void);
 /* Number of kernel launches issued through this handle so far (bench.py's gpu_launches). */
 int nrc_b200_launch_count(nrc_b200_handle h, uint64_t* count);

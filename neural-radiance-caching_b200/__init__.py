@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "nrc_b200_last_error", "nrc_b200_launch_count", "nrc_b200_debug_train_timeline", "nrc_b200_dp_export", "nrc_b200_dp_connect", "nrc_b200_train_dp",
     "nrc_b200_accumulate_render_radiance", "nrc_b200_propagate_train_radiance", "nrc_b200_permutation",
     "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_train_batches", "nrc_b200_adjust_tile_size", "nrc_b200_update",
-    "nrc_b200_release", "nrc_b200_set_accumulator", "nrc_b200_dp_connect_local", "nrc_b200_permute_train_data_with",
+    "nrc_b200_debug_l2_read_bandwidth", "nrc_b200_release", "nrc_b200_set_accumulator", "nrc_b200_dp_connect_local", "nrc_b200_permute_train_data_with",
 ]
 ACC_FP32, ACC_FP16 = 0, 1         # nrc_b200_set_accumulator
 
@@ -115,6 +115,7 @@ def lib():
         L.nrc_b200_dp_connect.argtypes = [vp, i32, i32, vp]
         L.nrc_b200_train_dp.argtypes = [vp, vp, vp, u32, u32, vp, P(f32)]
         L.nrc_b200_release.argtypes = [vp]
+        L.nrc_b200_debug_l2_read_bandwidth.argtypes = [u64, i32, P(f32)]
         L.nrc_b200_set_accumulator.argtypes = [vp, i32]
         L.nrc_b200_dp_connect_local.argtypes = [P(vp), i32]
         L.nrc_b200_permute_train_data_with.argtypes = [vp, vp, vp, vp, vp, i32, vp]
@@ -171,6 +172,13 @@ def dp_connect_local(networks):
     """Connects the data-parallel exchange between Network objects of THIS process (one per GPU), rank = list index."""
     arr = (ctypes.c_void_p * len(networks))(*[n._h for n in networks])
     _check(lib().nrc_b200_dp_connect_local(arr, len(networks)))
+
+
+def l2_read_bandwidth(nbytes=32 << 20, reps=20):
+    """Measured GB/s the SMs read from an L2-resident buffer (bench.py's gather-roofline denominator)."""
+    v = ctypes.c_float()
+    _check(lib().nrc_b200_debug_l2_read_bandwidth(int(nbytes), int(reps), ctypes.byref(v)))
+    return v.value
 
 
 def permutation(i, seed):

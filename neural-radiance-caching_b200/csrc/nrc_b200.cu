@@ -805,6 +805,13 @@ int nrc_b200_debug_train_timeline(nrc_b200_handle h, int enable, long long* dst_
     return NRC_B200_OK;
 }
 
+// Measurement aid for bench.py: read bandwidth (GB/s) the SMs get from an L2-resident buffer of `bytes` on the current device.
+int nrc_b200_debug_l2_read_bandwidth(uint64_t bytes, int reps, float* gbs) {
+    if (!gbs || bytes < (1u << 20) || reps < 1) return fail(NRC_B200_ERR_INVALID, "bad argument");
+    CU(l2_read_probe((size_t)bytes & ~(size_t)15, reps, gbs));
+    return NRC_B200_OK;
+}
+
 int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d) {
     if (!h || !loss_d || h->destroyed) return fail(NRC_B200_ERR_INVALID, "bad handle/argument");
     *loss_d = h->loss_d;

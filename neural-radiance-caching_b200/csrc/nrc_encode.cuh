@@ -334,8 +334,10 @@ __device__ __forceinline__ uint64_t entry_addr(uint64_t table, uint32_t idx) {  
     asm("mad.wide.u32 %0, %1, 4, %2;" : "=l"(a) : "r"(idx), "l"(table));
     return a;
 }
-// SMEM: the level's table has been staged in shared memory (smem_table = its 32-bit shared address)
-template <bool SMEM>
+// SMEM: the level's table has been staged in shared memory (smem_table = its 32-bit shared address).
+// NC: read-only (ld.global.nc) loads -- query kernel; false: plain loads -- the training kernel updates the table later in the
+// same launch.
+template <bool SMEM, bool NC = true>
 __device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table_ptr, uint32_t smem_table, uint32_t size_mask, uint32_t sy,
                                            uint32_t sz, float scale, bool dense, float x, float y, float z) {
     constexpr uint32_t kMagicBits = 0x4B400000u;                       // bit pattern of 1.5 * 2^23
@@ -399,8 +401,13 @@ __device__ __forceinline__ void grid_issue(GridFetch& F, const __half2* table_pt
             asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "r"(smem_table + i0[j] * 4u));
             asm volatile("ld.shared.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "r"(smem_table + i1[j] * 4u));
         } else {
-            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(entry_addr(table, i0[j])));
-            asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(entry_addr(table, i1[j])));
+            if constexpr (NC) {
+                asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(entry_addr(table, i0[j])));
+                asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(entry_addr(table, i1[j])));
+            } else {
+                asm volatile("ld.global.b32 %0, [%1];" : "=r"(F.v[2 * j]) : "l"(entry_addr(table, i0[j])) : "memory");
+                asm volatile("ld.global.b32 %0, [%1];" : "=r"(F.v[2 * j + 1]) : "l"(entry_addr(table, i1[j])) : "memory");
+            }
         }
     }
 #endif
@@ -429,10 +436,10 @@ __device__ __forceinline__ uint32_t grid_consume(const GridFetch& F) {
     }
     return *reinterpret_cast<uint32_t*>(&acc);
 }
-template <int L, bool SMEM0>
+template <int L, bool SMEM0, bool NC = true>
 __device__ __forceinline__ void grid_issue_level(GridFetch& F, const float (&q)[15], const __half2* grid, uint32_t smem_level0, const GridMeta& gm) {
     const uint32_t size = gm.offset[L + 1] - gm.offset[L];
-    grid_issue<(L == 0 && SMEM0)>(F, grid + gm.offset[L], smem_level0, size - 1, gm.stride_y[L], gm.stride_z[L], gm.scale[L],
+    grid_issue<(L == 0 && SMEM0), NC>(F, grid + gm.offset[L], smem_level0, size - 1, gm.stride_y[L], gm.stride_z[L], gm.scale[L],
                                   (gm.dense_mask >> L) & 1, q[0], q[1], q[2]);
 }
 
@@ -486,7 +493,37 @@ __device__ __forceinline__ void encode_frequency_half(const float (&q)[15], uint
         for (int i = 13; i < 20; ++i) e[i] = 0x3C003C00u;
     }
 }
-// Hash (8 chunks): HF0 = the 16 grid levels (features 0..31); HF1 = one-blob, albedos, pad (features 32..63).
+// Hash, training kernel: the two threads of a sample split the gather -- thread HF runs levels 8 HF .. 8 HF + 7 through the
+// pipelined gather (plain loads) and a part of the cheap features.  Output: four 16-byte chunks of the K-major feature row,
+// chunk ids in `ids` (chunk c = features 8c .. 8c+7: grid levels 4c .. 4c+3 for c < 4, one-blob pairs for c = 4..6, albedos + pad 7).
+//   HF0: chunks 0, 1 (levels 0..7), 4, 5 (one-blob of dims 0..3)      HF1: chunks 2, 3 (levels 8..15), 6 (dims 4, 5), 7
+template <int L0, int L>
+__device__ __forceinline__ void hash_half_levels(GridFetch (&F)[2], uint32_t (&e)[16], const float (&q)[15], const __half2* grid, const GridMeta& gm) {
+    if constexpr (L < L0 + 8) {
+        if constexpr (L + 1 < L0 + 8) grid_issue_level<L + 1, false, false>(F[(L + 1) & 1], q, grid, 0u, gm);
+        e[L - L0] = grid_consume(F[L & 1]);
+        hash_half_levels<L0, L + 1>(F, e, q, grid, gm);
+    }
+}
+template <int HF>
+__device__ __forceinline__ void encode_hash_split(const float (&q)[15], const __half2* grid, const GridMeta& gm, uint32_t (&e)[16], int (&ids)[4]) {
+    GridFetch F[2];
+    grid_issue_level<8 * HF, false, false>(F[0], q, grid, 0u, gm);
+    hash_half_levels<8 * HF, 8 * HF>(F, e, q, grid, gm);
+    if constexpr (HF == 0) {
+        ids[0] = 0; ids[1] = 1; ids[2] = 4; ids[3] = 5;
+        oneblob_pair<false>(q[3], q[4], e + 8);
+        oneblob_pair<false>(q[5], q[6], e + 12);
+    } else {
+        ids[0] = 2; ids[1] = 3; ids[2] = 6; ids[3] = 7;
+        oneblob_pair<false>(q[7], q[8], e + 8);
+        e[12] = pack_h2(q[9], q[10]);
+        e[13] = pack_h2(q[11], q[12]);
+        e[14] = pack_h2(q[13], q[14]);
+        e[15] = 0x3C003C00u;
+    }
+}
+// Round-1 form (kept for A/B builds): HF0 = the 16 grid levels (features 0..31); HF1 = one-blob, albedos, pad (features 32..63).
 template <int HF>
 __device__ __forceinline__ void encode_hash_half(const float (&q)[15], const __half2* grid,
                                                  const GridMeta& gm, uint32_t (&e)[16]) {

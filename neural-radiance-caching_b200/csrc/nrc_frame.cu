@@ -83,6 +83,50 @@ nrc_permute_with_kernel(const float* __restrict__ q_src, const float* __restrict
     else t_dst[d * 3u + (c - 15u)] = __ldg(t_src + (size_t)s * 3u + (c - 15u));
 }
 
+// Measurement aid (bench.py's L2 roofline denominator): every thread sums 16-byte L1-bypassing loads over an L2-resident buffer.
+__global__ void __launch_bounds__(256)
+nrc_l2_read_probe_kernel(const float4* __restrict__ buf, size_t n_vec, int reps, float* sink) {
+    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int r = 0; r < reps; ++r)
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += 4 * stride) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = i + u * stride < n_vec ? __ldcg(buf + i + u * stride) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w; }
+        }
+    if (acc.x + acc.y + acc.z + acc.w == 123.456f) *sink = acc.x;     // never true: keeps the loads alive
+}
+cudaError_t l2_read_probe(size_t bytes, int reps, float* gbs) {
+    float4* buf = nullptr; float* sink = nullptr;
+    cudaError_t e = cudaMalloc(&buf, bytes);
+    if (e != cudaSuccess) return e;
+    cudaMalloc(&sink, 4);
+    cudaMemset(buf, 0, bytes);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    nrc_l2_read_probe_kernel<<<sms * 8, 256>>>(buf, bytes / 16, 2, sink);       // warm-up: brings the buffer into L2
+    float best = 1e30f;
+    for (int it = 0; it < 5; ++it) {
+        cudaEventRecord(a);
+        nrc_l2_read_probe_kernel<<<sms * 8, 256>>>(buf, bytes / 16, reps, sink);
+        cudaEventRecord(b);
+        cudaEventSynchronize(b);
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, a, b);
+        if (ms < best) best = ms;
+    }
+    e = cudaGetLastError();
+    *gbs = (float)((double)bytes * reps / (best * 1e-3) / 1e9);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    cudaFree(buf); cudaFree(sink);
+    return e;
+}
+
 cudaError_t launch_accumulate(const float* radiance, const float* throughput, float* out4, uint32_t n_pixels, int mode,
                               uint32_t iteration_index, cudaStream_t stream) {
     if (n_pixels == 0) return cudaSuccess;

@@ -28,6 +28,12 @@ namespace nrcb {
 #ifndef NRC_HASH_GATHER
 #define NRC_HASH_GATHER 1         // 0: level after level with 8 loads each (round-1 form, A/B builds); 1: pipelined gather (nrc_encode.cuh)
 #endif
+#ifndef NRC_HASH_DEPTH
+#define NRC_HASH_DEPTH 2          // levels of the hash gather whose loads are in flight per thread.  Measured (A/B builds hashd3 / hashd4,
+                                  // which read the twelve non-position inputs only after the gather to pay for the registers): 529 / 540 /
+                                  // 531 us per 2K frame for 2 / 3 / 4 -- the gather is bound by the L1TEX tag rate (8 cycles per divergent
+                                  // LDG), not by latency, once two levels overlap
+#endif
 #ifndef NRC_HASH_SMEM0
 #define NRC_HASH_SMEM0 0          // 1: grid level 0 staged in shared memory (A/B builds: slower, it takes L1 capacity from the fine levels)
 #endif
@@ -102,22 +108,33 @@ __device__ __forceinline__ void issue_layer(uint32_t sbase, uint32_t a0, uint32_
 // Hash encode of one query straight into the TMEM A operand (32 words = 64 fp16 features at columns tA .. tA+31): the 16 grid
 // levels are software-pipelined (level l+1's loads in flight during level l's FMA chain, nrc_encode.cuh) and leave for TMEM in
 // chunks of 8 words, so at most 8 result words + two levels of pending loads are live.
-template <int L>
-__device__ __forceinline__ void hash_levels_pipelined(GridFetch (&F)[2], uint32_t (&w)[8], const float (&q)[15], const __half2* grid,
+template <int L, int D>
+__device__ __forceinline__ void hash_levels_pipelined(GridFetch (&F)[D], uint32_t (&w)[8], const float (&q)[15], const __half2* grid,
                                                       uint32_t smem_l0, const GridMeta& gm, uint32_t tA) {
     if constexpr (L < 16) {
-        if constexpr (L + 1 < 16) grid_issue_level<L + 1, NRC_HASH_SMEM0 != 0>(F[(L + 1) & 1], q, grid, smem_l0, gm);
-        w[L & 7] = grid_consume(F[L & 1]);
+        if constexpr (L + D - 1 < 16) grid_issue_level<L + D - 1, NRC_HASH_SMEM0 != 0>(F[(L + D - 1) % D], q, grid, smem_l0, gm);
+        w[L & 7] = grid_consume(F[L % D]);
         if constexpr ((L & 7) == 7) tmem_st8(tA + (L >> 3) * 8, w);
-        hash_levels_pipelined<L + 1>(F, w, q, grid, smem_l0, gm, tA);
+        hash_levels_pipelined<L + 1, D>(F, w, q, grid, smem_l0, gm, tA);
     }
 }
-__device__ __forceinline__ void encode_hash_to_tmem(const float (&q)[15], const __half2* grid, uint32_t smem_l0, const GridMeta& gm, uint32_t tA) {
-    GridFetch F[2];
+template <int L, int D>
+__device__ __forceinline__ void hash_prologue(GridFetch (&F)[D], const float (&q)[15], const __half2* grid, uint32_t smem_l0, const GridMeta& gm) {
+    if constexpr (L < D - 1) {
+        grid_issue_level<L, NRC_HASH_SMEM0 != 0>(F[L], q, grid, smem_l0, gm);
+        hash_prologue<L + 1, D>(F, q, grid, smem_l0, gm);
+    }
+}
+// Grid part (words 0..15): needs q[0..2] only.  NRC_HASH_DEPTH levels of loads are in flight per thread.
+__device__ __forceinline__ void encode_hash_grid_to_tmem(const float (&q)[15], const __half2* grid, uint32_t smem_l0, const GridMeta& gm, uint32_t tA) {
+    GridFetch F[NRC_HASH_DEPTH];
     uint32_t w[8];
-    grid_issue_level<0, NRC_HASH_SMEM0 != 0>(F[0], q, grid, smem_l0, gm);
-    hash_levels_pipelined<0>(F, w, q, grid, smem_l0, gm, tA);
-    uint32_t ob[12];                                                                          // one-blob: words 16..27
+    hash_prologue<0, NRC_HASH_DEPTH>(F, q, grid, smem_l0, gm);
+    hash_levels_pipelined<0, NRC_HASH_DEPTH>(F, w, q, grid, smem_l0, gm, tA);
+}
+// One-blob, albedos, pad (words 16..31): needs q[3..14].
+__device__ __forceinline__ void encode_hash_rest_to_tmem(const float (&q)[15], uint32_t tA) {
+    uint32_t ob[12];
 #pragma unroll
     for (int d = 0; d < 6; d += 2) oneblob_pair<false>(q[3 + d], q[4 + d], ob + 2 * d);
     {
@@ -376,15 +393,33 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
         for (; t < n_tiles; t += tile_stride) {
             mbar_wait(&in_full[g], ph_in); ph_in ^= 1;
             float q[15];
+            if constexpr (ENC == 1 && NRC_HASH_GATHER != 0 && NRC_HASH_DEPTH > 2) {
+                // deeper pipelines: only the position is needed for the gather; the other twelve inputs are read from the stage
+                // AFTER it, so their registers carry more pending loads instead (the stage is released, and the next tile's bulk
+                // copy issued, only then: it still has the six layers of this tile to land)
+#pragma unroll
+                for (int i = 0; i < 3; ++i) q[i] = s_in[row * 15 + i];
+                encode_hash_grid_to_tmem(q, grid, smem_u32(smem + L::kL0Off), gm, tA);
+#pragma unroll
+                for (int i = 3; i < 15; ++i) q[i] = s_in[row * 15 + i];
+                fence_proxy_async_smem();                    // order these generic reads before the next bulk write
+                bar_sync_id(bar_d);                          // everyone holds its query: the stage is free
+                if (t + tile_stride < n_tiles) load_tile(t + tile_stride, par ^ 1);
+                encode_hash_rest_to_tmem(q, tA);
+            } else {
 #pragma unroll
             for (int i = 0; i < 15; ++i) q[i] = s_in[row * 15 + i];
             fence_proxy_async_smem();                        // order these generic reads before the next bulk write
             bar_sync_id(bar_d);                              // everyone holds its query: the stage is free
             if (t + tile_stride < n_tiles) load_tile(t + tile_stride, par ^ 1);
+            }
 
             // ---- encode -> A operand of the input layer (its previous contents were consumed long ago)
             if constexpr (ENC == 1 && NRC_HASH_GATHER != 0) {
-                encode_hash_to_tmem(q, grid, smem_u32(smem + L::kL0Off), gm, tA);
+                if constexpr (NRC_HASH_DEPTH <= 2) {
+                    encode_hash_grid_to_tmem(q, grid, smem_u32(smem + L::kL0Off), gm, tA);
+                    encode_hash_rest_to_tmem(q, tA);
+                }
             } else {
                 uint32_t e[E / 2];
                 if constexpr (ENC == 0) encode_frequency(q, e);

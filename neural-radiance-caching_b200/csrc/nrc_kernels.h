@@ -107,4 +107,7 @@ cudaError_t launch_permute(const float* q_src, const float* t_src, float* q_dst,
 cudaError_t launch_permute_with(const float* q_src, const float* t_src, float* q_dst, float* t_dst, const int* permutation,
                                 uint32_t num_records, cudaStream_t stream);
 
+// measurement aid: read bandwidth of an L2-resident buffer (GB/s)
+cudaError_t l2_read_probe(size_t bytes, int reps, float* gbs);
+
 }  // namespace nrcb

@@ -270,6 +270,9 @@ __device__ __forceinline__ void grid_arrive(const TrainArgs& a, uint32_t tile) {
 #endif
 }
 
+#ifndef NRCB_HASH_SPLIT_ENCODE
+#define NRCB_HASH_SPLIT_ENCODE 1   // Hash training encode: 8 levels per thread of a sample, pipelined gather (0: round-1 form)
+#endif
 #ifndef NRCB_SCATTER_AGG
 #define NRCB_SCATTER_AGG 1
 #endif
@@ -424,7 +427,16 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
 #pragma unroll
             for (int c = 0; c < 3; ++c) tg[c] = __ldg(a.targets + (size_t)src_row * 3 + c);
         }
-        {
+        if constexpr (ENC == 1 && NRCB_HASH_SPLIT_ENCODE) {
+            // both threads of a sample gather: 8 levels each, next level's loads in flight during the current FMA chain
+            const __half2* grid = reinterpret_cast<const __half2*>(a.params + NMLP);
+            uint32_t e[16];
+            int ids[4];
+            if (hf == 0) encode_hash_split<0>(q, grid, gm, e, ids); else encode_hash_split<1>(q, grid, gm, e, ids);
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                *reinterpret_cast<uint4*>(row_chunk(smem + L::kX, row, ids[c])) = make_uint4(e[4 * c], e[4 * c + 1], e[4 * c + 2], e[4 * c + 3]);
+        } else {
             uint32_t e[E / 4];
             if constexpr (ENC == 0) {
                 if (hf == 0) encode_frequency_half<0>(q, e); else encode_frequency_half<1>(q, e);

@@ -65,10 +65,17 @@ def test_dp_fused_matches_nccl_and_single_gpu(pkg, synth, tmp_path, enc):
         ref.append(net.train(torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda(), want_loss=True))
     single = net.get_params(pkg.PARAMS_MASTER_F32)
     net.destroy()
+    lr = 1e-3 if enc == 0 else 1e-2
+    nm = 22528 if enc == 0 else 21504
     for mode in ("nccl", "fused"):
         assert np.allclose(res[mode][0]["losses"], ref, rtol=2e-3), (mode, res[mode][0]["losses"], ref)
-        nm = 22528 if enc == 0 else 21504
-        assert np.mean(np.abs(res[mode][0]["master"][:nm] - single[:nm]) <= 2e-3) > 0.99
-    if enc == 0:   # same summation order in both DP modes (rank-ordered sums of deterministic per-rank gradients)
-        assert np.array_equal(res["nccl"][0]["master"], res["fused"][0]["master"]) or \
-            np.mean(res["nccl"][0]["master"] == res["fused"][0]["master"]) > 0.98
+        # 6 steps move a weight by at most 6 lr.  Data parallel and single GPU sum the same 128 per-tile partials in a different
+        # association (rank by rank vs strided groups), so they agree to a small fraction of ONE step: measured <= 0.03 lr
+        # (Frequency) / 0.1 lr (Hash: fp32 atomics in the grid gradient) at the maximum, bit-identical for most weights.
+        d = np.abs(res[mode][0]["master"][:nm] - single[:nm])
+        print(f"[dp {mode} enc {enc}] max |w_dp - w_single| = {d.max():.3e} ({d.max() / lr:.4f} lr), identical {np.mean(d == 0):.3f}, "
+              f"within 0.01 lr {np.mean(d <= 0.01 * lr):.4f}")
+        assert d.max() <= 0.25 * lr and np.mean(d <= 0.02 * lr) > 0.99
+    if enc == 0:   # same per-rank partial sums, added in rank order by both exchanges: bit-identical
+        assert np.array_equal(res["nccl"][0]["master"], res["fused"][0]["master"])
+        assert np.array_equal(res["nccl"][0]["ema"], res["fused"][0]["ema"])

@@ -1,6 +1,10 @@
 """Summarises ncu artefacts brought back in gpurun_out/ into small text files for profiles/.
 usage: python tools/ncu_summary.py launches <csv>            -> per-kernel totals and shares
-       python tools/ncu_summary.py rep <file.ncu-rep>        -> key counters + SASS opcode mix"""
+       python tools/ncu_summary.py rep <file.ncu-rep>        -> key counters + SASS opcode mix
+       python tools/ncu_summary.py traffic <file.ncu-rep> <key> <summary.txt> [json]
+                                                             -> dram__bytes_read.sum + dram__bytes_write.sum (and, key + "_l2",
+                                                                lts__t_sectors.sum * 32) of the captured launch into
+                                                                profiles/r02_traffic.json, which bench.py reads for roofline.traffic"""
 import collections
 import csv
 import io
@@ -77,5 +81,30 @@ def rep(path):
         print(f"{k:12s} {v:12d} {100 * v / tot:5.1f}%  samples {samp[k]}")
 
 
+def _to_bytes(value, unit):
+    v = float(value.replace(",", ""))
+    u = unit.strip().lower()
+    return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9, "sector": 32}.get(u, 1)
+
+
+def traffic(path, key, source, out=None):
+    import json
+    import os
+    out = out or os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r02_traffic.json")
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    h, units, r = rows[0], rows[1], rows[2]
+
+    def get(name):
+        i = [k for k, n in enumerate(h) if n == name or n.endswith("." + name)][0]
+        return _to_bytes(r[i], units[i])
+    d = json.load(open(out)) if os.path.exists(out) else {}
+    d[key] = {"bytes": get("dram__bytes_read.sum") + get("dram__bytes_write.sum"), "source": source,
+              "what": "dram__bytes_read.sum + dram__bytes_write.sum of one launch (ncu --set full)"}
+    d[key + "_l2"] = {"bytes": get("lts__t_sectors.sum"), "source": source, "what": "lts__t_sectors.sum x 32 B of one launch (ncu --set full)"}
+    json.dump(d, open(out, "w"), indent=1)
+    print(key, d[key], d[key + "_l2"])
+
+
 if __name__ == "__main__":
-    {"launches": launches, "rep": rep}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "rep": rep, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])
