@@ -463,7 +463,8 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.partials = h->partials; a.grid_grad = h->grid_grad; a.loss_partials = h->loss_partials;
     a.grad_f32 = h->grad_f32; a.loss_out = h->loss_d;
     a.barrier_counter = h->barrier_counter;
-    a.barrier_target = h->barrier_total + train_barrier_arrivals(n_local);   // top counter once every CTA reached the FIRST barrier
+    a.wide_grid = (h->encoding == NRC_B200_HASH && h->num_sms >= (int)kWideGrid) ? 1 : 0;
+    a.barrier_target = h->barrier_total + train_barrier_arrivals(n_local, a.wide_grid);   // top counter once every CTA reached the FIRST barrier
     a.n_params = h->n_params; a.n_mlp = h->n_mlp;
     a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
     a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
@@ -498,7 +499,7 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
 static int launch_and_commit(Net* h, const TrainArgs& a, uint32_t n_barriers) {
     CU(launch_train_step(h->encoding, a, h->gm, h->stream));
     h->launches += 1;
-    h->barrier_total += n_barriers * train_barrier_arrivals(a.n_local);
+    h->barrier_total += n_barriers * train_barrier_arrivals(a.n_local, a.wide_grid);
     if (a.apply) {
         h->step += a.n_steps;
         if (a.dp_world > 1) h->dp_seq += a.n_steps;
@@ -579,7 +580,7 @@ static int dp_alloc(Net* h) {
     // per (parity, source rank) row: [(n_mlp + 1 -> 32) tagged float2 slots | n_grid floats]  (nrc_train.cu phase 3)
     h->x_stride = 2 * ((h->n_mlp + 1 + 31) / 32 * 32) + ((h->n_params - h->n_mlp) + 31) / 32 * 32;
     h->xbuf_bytes = (size_t)2 * kMaxDpRanks * h->x_stride * sizeof(float);
-    const size_t flag_bytes = (size_t)2 * kMaxDpRanks * 128 * sizeof(uint32_t);
+    const size_t flag_bytes = (size_t)2 * kMaxDpRanks * kDpFlagSlots * sizeof(uint32_t);
     CU(cudaMalloc(&h->dp_local, h->xbuf_bytes + flag_bytes));
     CU(cudaMemset(h->dp_local, 0, h->xbuf_bytes + flag_bytes));
     CU(cudaDeviceSynchronize());

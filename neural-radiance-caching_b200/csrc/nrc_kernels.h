@@ -56,6 +56,7 @@ struct TrainArgs {
     // of `in` / `targets` (fused shuffle: destination indices perm_base + s*n_local + ...), writes its loss to
     // loss_out[s]; two grid barriers per step (gradients complete / weights updated), the last one omitted.
     uint32_t n_steps;
+    int wide_grid;                   // Hash on a 148-SM device: the launch has 148 CTAs (train_grid)
     long long* timeline;             // optional [n_tiles][8] clock64 stamps of the phases (debug), or nullptr
     // Data-parallel exchange fused into phase 3 (dp_world > 1, apply = 1): every rank pushes its slice gradients into
     // row `dp_rank` of EVERY peer's exchange buffer through NVLink peer pointers and sums the rows it received in rank
@@ -76,18 +77,28 @@ struct TrainArgs {
     uint32_t dp_timeout_ms;          // context survives, the next API call reports the error)
 };
 constexpr int kMaxDpRanks = 8;
-// CTAs of a step launch: one per 128-sample tile, but never fewer than 128 -- short data-parallel shards keep the gradient
-// reduction / optimizer phase 128 slices wide (the extra CTAs skip phase 1).  The grid barrier counts this many arrivals.
-inline __host__ __device__ uint32_t train_grid(uint32_t n_local) { const uint32_t t = n_local / 128; return t < 128 ? 128 : t; }
-// Two-level grid barrier (nrc_train.cu grid_arrive): CTAs arrive in groups of kBarrierFan on per-group counters, the last
-// arriver of a group on the top counter; one barrier instance adds this many arrivals to the top counter.
 #ifndef NRCB_BARRIER_TREE
 #define NRCB_BARRIER_TREE 0      // measured: the two dependent L2 round trips cost more than the serialised arrivals (+1.3 us per barrier, profiles/r02_ab_variants.json)
 #endif
+// CTAs of a step launch: one per 128-sample tile, but never fewer than 128 -- short data-parallel shards keep the gradient
+// reduction / optimizer phase 128 slices wide (the extra CTAs skip phase 1).  The grid barrier counts this many arrivals.
+// Hash (wide = 1): 148 CTAs -- the 20 CTAs without a data tile only take part in phase 3, whose pass over the 991 232 grid
+// parameters (26 B each) then runs on every SM of a B200 instead of 128 of them.
+#ifndef NRCB_HASH_GRID148
+#define NRCB_HASH_GRID148 1
+#endif
+constexpr uint32_t kWideGrid = 148;
+constexpr uint32_t kDpFlagSlots = 160;   // per (parity, source rank): one flag per gradient slice (= CTA), >= the widest grid
+inline __host__ __device__ uint32_t train_grid(uint32_t n_local, int wide = 0) {
+    const uint32_t t = n_local / 128, g = t < 128 ? 128 : t;
+    return (NRCB_HASH_GRID148 && !NRCB_BARRIER_TREE && wide && g < kWideGrid) ? kWideGrid : g;
+}
+// Two-level grid barrier (nrc_train.cu grid_arrive): CTAs arrive in groups of kBarrierFan on per-group counters, the last
+// arriver of a group on the top counter; one barrier instance adds this many arrivals to the top counter.
 constexpr uint32_t kBarrierFan = 16;
 constexpr uint32_t kBarrierWords = 32 * (1 + 16);   // top counter + up to 16 group counters, 128 bytes apart
-inline __host__ __device__ uint32_t train_barrier_arrivals(uint32_t n_local) {
-    return NRCB_BARRIER_TREE ? train_grid(n_local) / kBarrierFan : train_grid(n_local);
+inline __host__ __device__ uint32_t train_barrier_arrivals(uint32_t n_local, int wide = 0) {
+    return NRCB_BARRIER_TREE ? train_grid(n_local, wide) / kBarrierFan : train_grid(n_local, wide);
 }
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream);
 

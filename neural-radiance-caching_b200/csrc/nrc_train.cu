@@ -279,6 +279,12 @@ __device__ __forceinline__ void grid_arrive(const TrainArgs& a, uint32_t tile) {
 #ifndef NRCB_AGG_LEVELS
 #define NRCB_AGG_LEVELS 8     // coarsest levels whose scatter is pre-aggregated per tile in shared memory
 #endif
+#ifndef NRCB_SCATTER_V2
+#define NRCB_SCATTER_V2 1     // one rolled pass over all levels between two barriers, one table per coarse level (0: a table sweep + 3 barriers per coarse level, unrolled)
+#endif
+#ifndef NRCB_AGG_SLOTS
+#define NRCB_AGG_SLOTS 1024   // slots per coarse level (a tile sends 1024 corner updates to a level)
+#endif
 // ---------------------------------------------------------------- the step kernel
 template <int ENC, bool MULTI>   // MULTI: a.n_steps optimizer steps in this launch (separate instantiation: the loop costs the
 __global__ void __launch_bounds__(kTrainThreads, 1)   // single-step Hash kernel registers in its scatter loop)
@@ -295,12 +301,13 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     uint64_t* w_full = bars + 3;    // bulk copy of the weight image
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
     float* warp_loss = reinterpret_cast<float*>(bars + 5);   // [4]
+    uint32_t* s_lvmax = reinterpret_cast<uint32_t*>(bars + 8);   // [8] Hash scatter: per coarse level, tile maximum of |dL/dy| (float bits)
 
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // provably warp-uniform
     const uint32_t tile = blockIdx.x;
     const uint32_t n_tiles = gridDim.x;              // CTAs = gradient slices of phase 3 (>= data tiles)
     const uint32_t n_data = a.n_local / kTT;         // 128-sample tiles of this launch: CTAs [0, n_data) run phase 1
-    const uint32_t n_arrivals = train_barrier_arrivals(a.n_local);   // what one barrier instance adds to the counter everybody polls
+    const uint32_t n_arrivals = train_barrier_arrivals(a.n_local, a.wide_grid);   // what one barrier instance adds to the counter everybody polls
     const bool has_tile = tile < n_data;
     const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0 && a.perm_n == 0;   // bulk copy needs a contiguous tile
     uint32_t s = 0;                 // optimizer step within this launch
@@ -310,6 +317,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     if (tid == 0) {
         mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1);
         fence_mbar_init();
+        for (int i = 0; i < 8; ++i) s_lvmax[i] = 0;
     }
     if (warp == kWorkerWarps) tmem_alloc(tmem_slot, 512);
     tc_fence_before();
@@ -561,6 +569,137 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         wait_mma();
         stamp(3);
         if (warp == 0 && lane == 0) a.loss_partials[tile] = (warp_loss[0] + warp_loss[1]) + (warp_loss[2] + warp_loss[3]);
+#if NRCB_SCATTER_V2
+        if constexpr (ENC == 1) {
+            // Grid gradient scatter (grid.h:252-255,301-319), second form: ONE pass over the 16 levels between TWO barriers.
+            // Both threads of a sample walk all levels; half hf takes the four corners with dz = hf.  The kAgg coarsest levels
+            // are pre-aggregated per tile (a concentrated scene sends the 1024 corner updates of a coarse level to a few dozen
+            // entries, which serialises global atomics in L2): every such level owns a direct-mapped table of kSlots
+            // (tag, fixed-point accumulator pair) slots in the dead activation / delta area, so no level waits for another;
+            // the first form paid three CTA barriers and a table sweep per coarse level.
+            constexpr int kAgg = NRCB_AGG_LEVELS;
+            constexpr uint32_t kSlots = NRCB_AGG_SLOTS, kEmpty = 0xFFFFFFFFu;
+            static_assert(kAgg <= 8 && kAgg * kSlots * 12 <= 7 * 16384 && (kSlots & (kSlots - 1)) == 0, "tables live in kH .. kDelta");
+            uint32_t* s_tag = reinterpret_cast<uint32_t*>(smem + L::kH);                       // [kAgg][kSlots]
+            int* s_acc = reinterpret_cast<int*>(smem + L::kH + kAgg * kSlots * 4);             // [kAgg][kSlots][2] fixed point
+            const uint32_t wtid = warp * 32 + lane;                                            // 0..255 over the 8 worker warps
+            auto workers_sync = [] { asm volatile("bar.sync 1, 256;" ::: "memory"); };
+            const bool g16 = a.grid_grad_fp16 != 0;   // reference arithmetic: half products, half2 atomics, no aggregation
+            auto grad_of = [&](uint32_t w) {   // dL/d(feature) of this sample, rounded to fp16 like the reference's dL_dy
+                return acc16 ? __half2float(__ushort_as_half((unsigned short)(w & 0xFFFFu))) : __half2float(__float2half_rn(__uint_as_float(w)));
+            };
+            if (!g16) {
+                uint32_t vc[16];                       // the coarse levels' gradients: per-level maximum over the tile
+                tmem_ld16(tq + kAcc, vc);
+                uint4* t4 = reinterpret_cast<uint4*>(s_tag);
+                for (uint32_t i = wtid; i < kAgg * kSlots / 4; i += 256) t4[i] = make_uint4(kEmpty, kEmpty, kEmpty, kEmpty);
+                uint4* a4 = reinterpret_cast<uint4*>(s_acc);
+                for (uint32_t i = wtid; i < kAgg * kSlots / 2; i += 256) a4[i] = make_uint4(0u, 0u, 0u, 0u);
+                tmem_wait_ld();
+                if (hf == 0) {
+#pragma unroll
+                    for (int lv = 0; lv < kAgg; ++lv) {
+                        const uint32_t mx = __reduce_max_sync(0xffffffffu, max(__float_as_uint(fabsf(grad_of(vc[2 * lv]))), __float_as_uint(fabsf(grad_of(vc[2 * lv + 1])))));
+                        if (lane == 0) atomicMax(&s_lvmax[lv], mx);
+                    }
+                }
+                workers_sync();
+            }
+            // The level loop is NOT unrolled on purpose: a CTA walks this code once per step, so an unrolled body (16 levels x
+            // 4 corners x 3 paths) is paid for in instruction fetches -- ncu attributed 69 % of the stall samples of the unrolled
+            // scatter to `no instruction`.  The level's two gradient columns come straight from TMEM.
+            // Coarse (shared-memory) and fine (global) levels alternate: 0, 8, 1, 9, ...
+#pragma unroll 1
+            for (int it = 0; it < 16; ++it) {
+                const int lv = (it & 1) ? 8 + (it >> 1) : (it >> 1);
+                uint32_t gw[2];
+                tmem_ld2(tq + kAcc + 2 * lv, gw);
+                tmem_wait_ld();
+                const float g0 = grad_of(gw[0]), g1 = grad_of(gw[1]);
+                if (g0 == 0.0f && g1 == 0.0f) continue;
+                const bool agg_level = lv < kAgg && !g16;
+                const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
+                const bool dense = (gm.dense_mask >> lv) & 1;
+                float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
+                float p[3];
+                uint32_t gp[3];
+#pragma unroll
+                for (int d = 0; d < 3; ++d) {
+                    p[d] = fmaf(gm.scale[lv], q[d], 0.5f);
+                    const float fl = floorf(p[d]);
+                    gp[d] = (uint32_t)(int)fl;
+                    p[d] -= fl;
+                }
+                const float fz = hf ? p[2] : 1.0f - p[2];
+                const uint32_t cz = gp[2] + hf;
+                uint32_t idx[4];
+                float wgt[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    wgt[c] = (((c & 1) ? p[0] : 1.0f - p[0]) * ((c & 2) ? p[1] : 1.0f - p[1])) * fz;
+                    const uint32_t cx = gp[0] + (c & 1), cy = gp[1] + (c >> 1);
+                    idx[c] = (dense ? cx + cy * sy + cz * sz : cx ^ (cy * 2654435761u) ^ (cz * 805459861u)) & (size - 1);
+                }
+                if (g16) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        const __half2 prod = __hmul2(__float2half2_rn(wgt[c]), __floats2half2_rn(g0, g1));   // half x half, rounded to half
+                        uint32_t* gh = reinterpret_cast<uint32_t*>(a.grid_grad) + gm.offset[lv] + idx[c];     // half2 accumulators
+                        asm volatile("red.global.add.noftz.f16x2 [%0], %1;" ::"l"(gh), "r"(*reinterpret_cast<const uint32_t*>(&prod)) : "memory");
+                    }
+                    continue;
+                }
+                float v0[4], v1[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float wh = __half2float(__float2half_rn(wgt[c]));   // (GRAD_T)weight, grid.h:254
+                    v0[c] = wh * g0; v1[c] = wh * g1;
+                }
+                if (agg_level) {
+                    const uint32_t eb = max(s_lvmax[lv] >> 23, 24u);
+                    const float S = __uint_as_float((273u - eb) << 23);     // 20 bits below the level's largest |dL/dy|, 1024 terms of headroom
+                    uint32_t sl[4], old[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {   // the four claims are independent: all in flight before the first add
+                        sl[c] = lv * kSlots + (idx[c] & (kSlots - 1));
+                        old[c] = atomicCAS(&s_tag[sl[c]], kEmpty, idx[c]);
+                    }
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if (old[c] == kEmpty || old[c] == idx[c]) {
+                            atomicAdd(&s_acc[2 * sl[c]], __float2int_rn(v0[c] * S));
+                            atomicAdd(&s_acc[2 * sl[c] + 1], __float2int_rn(v1[c] * S));
+                        } else {     // slot taken by another entry of this level: straight to global memory
+                            asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx[c]), "f"(v0[c]), "f"(v1[c]) : "memory");
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c)
+                        asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * idx[c]), "f"(v0[c]), "f"(v1[c]) : "memory");
+                }
+            }
+            if (!g16) {   // flush: one global red per distinct entry the tile touched
+                workers_sync();
+                const uint4* t4 = reinterpret_cast<const uint4*>(s_tag);
+                for (uint32_t i = wtid; i < kAgg * kSlots / 4; i += 256) {
+                    const uint4 tg4 = t4[i];
+                    if ((tg4.x & tg4.y & tg4.z & tg4.w) == kEmpty) continue;
+                    const uint32_t tg_[4] = {tg4.x, tg4.y, tg4.z, tg4.w};
+                    const uint32_t lv = (4 * i) / kSlots;
+                    const uint32_t eb = max(s_lvmax[lv] >> 23, 24u);
+                    const float Sinv = __uint_as_float((eb - 19u) << 23);
+                    float* gl = a.grid_grad + (size_t)gm.offset[lv] * 2;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (tg_[u] != kEmpty) {
+                            const int2 ac = *reinterpret_cast<const int2*>(&s_acc[2 * (4 * i + u)]);
+                            asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(gl + 2 * tg_[u]), "f"((float)ac.x * Sinv), "f"((float)ac.y * Sinv) : "memory");
+                        }
+                }
+            }
+        }
+#else
         if constexpr (ENC == 1) {
             // Grid gradient scatter (grid.h:252-255,301-319).  Both threads of a sample walk all 16 levels; half hf takes the
             // four corners with dz = hf, so the halves finish together (with levels split 8 / 8 the half that owned the
@@ -668,6 +807,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             level(std::integral_constant<int, 12>{}); level(std::integral_constant<int, 13>{});
             level(std::integral_constant<int, 14>{}); level(std::integral_constant<int, 15>{});
         }
+#endif
         if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
         {   // the last two accumulators: dW_in and dW_h1, all loads in flight before the wait
             constexpr int kInChunks = E / 16;                 // 5 (Frequency) / 4 (Hash)
@@ -692,7 +832,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     __threadfence();
     tc_fence_before();
     __syncthreads();
-    if (tid == 0) grid_arrive(a, tile);
+    if (tid == 0) {
+        grid_arrive(a, tile);
+        for (int i = 0; i < 8; ++i) s_lvmax[i] = 0;     // the scatter of this step is over: ready for the next step's maxima
+    }
     // slice `tile` of the parameters belongs to this CTA in phase 3: at most one matrix parameter per thread.  Its optimizer
     // state is loaded here, while the barrier is pending (the replicas of a data-parallel job hold identical state).
     const uint32_t S = ((NMLP + n_tiles - 1) / n_tiles + 3) & ~3u;     // parameters per CTA (multiple of 4)
@@ -832,7 +975,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 __threadfence_system();
                 __syncthreads();
                 if ((uint32_t)tid < R && (uint32_t)tid != me) {
-                    uint32_t* f = a.xflag[tid] + ((size_t)par * R + me) * 128 + tile;
+                    uint32_t* f = a.xflag[tid] + ((size_t)par * R + me) * kDpFlagSlots + tile;
                     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(seq) : "memory");
                 }
             }
@@ -861,7 +1004,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             }
             if constexpr (ENC == 1) {
                 if ((uint32_t)tid < R && (uint32_t)tid != me) {
-                    const uint32_t* w = a.xflag[me] + ((size_t)par * R + tid) * 128 + tile;
+                    const uint32_t* w = a.xflag[me] + ((size_t)par * R + tid) * kDpFlagSlots + tile;
                     uint32_t seen, spins = 0;
                     unsigned long long t0 = 0;
                     do {
@@ -938,7 +1081,7 @@ static cudaError_t launch_train_t(const TrainArgs& a, const GridMeta& gm, cudaSt
     const bool multi = a.apply && a.n_steps > 1;
     const void* fn = multi ? reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, true>)
                            : reinterpret_cast<const void*>(&nrc_train_step_kernel<ENC, false>);
-    return cudaLaunchCooperativeKernel(fn, dim3(train_grid(a.n_local)), dim3(kTrainThreads), args, L::kTotal, stream);
+    return cudaLaunchCooperativeKernel(fn, dim3(train_grid(a.n_local, a.wide_grid)), dim3(kTrainThreads), args, L::kTotal, stream);
 }
 cudaError_t launch_train_step(int encoding, const TrainArgs& a, const GridMeta& gm, cudaStream_t stream) {
     return encoding == 0 ? launch_train_t<0>(a, gm, stream) : launch_train_t<1>(a, gm, stream);
