@@ -94,6 +94,23 @@ int nrc_b200_train_grad(nrc_b200_handle h, const float* queries_d, const float* 
                         uint32_t n_global, float** grad_d, void* cu_stream);
 int nrc_b200_train_apply(nrc_b200_handle h, void* cu_stream, float* loss_h);
 
+/* nrc_b200_train_grad without any allocation or handle-owned scratch.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same kernel and arithmetic as nrc_b200_train_grad (forward + loss + backward + deterministic
+ * weight-gradient reduction, no optimizer step; the handle supplies the weights), but the per-tile gradient partials, the
+ * per-tile losses and the Hash grid-gradient accumulator live in a static __device__ array of the library (6.53 MiB, held by
+ * every GPU that loads the library until the process exits) and the results go to caller buffers:
+ *   grad_out_d  device, nrc_b200_n_params() floats: the fp32 gradient, loss-scaled (x128) like NRC_B200_GRAD_F32
+ *   loss_out_d  device, 1 float (may be NULL): the batch loss
+ * Limits (NRC_B200_ERR_INVALID with a message naming them otherwise): n_local a multiple of 128 and <= 4096 samples per call
+ * (nrc_b200_noalloc_limits reports it), log2_hashmap_size <= 15.  The call performs no cudaMalloc / cudaFree and never
+ * synchronises.  All calls on one device share the array, which keeps the last call's contents (what must start at zero is
+ * cleared on the call's stream): calls that overlap on the GPU -- other streams, other handles of the same device -- race on
+ * it and must be serialised by the caller.  It does not disturb a gradient pending for nrc_b200_train_apply. */
+int nrc_b200_train_grad_noalloc(nrc_b200_handle h, const float* queries_d, const float* targets_d, uint32_t n_local,
+                                uint32_t n_global, float* grad_out_d, float* loss_out_d, void* cu_stream);
+int nrc_b200_noalloc_limits(uint32_t* max_samples, uint64_t* scratch_bytes);
+
 /* Data-parallel training with the gradient all-reduce FUSED into the step kernel (peer stores + flags over NVLink;
  * one process per GPU, CUDA IPC).  Protocol: every rank calls nrc_b200_dp_export, the host all-gathers the
  * NRC_B200_IPC_HANDLE_BYTES-byte handles (any transport), every rank calls nrc_b200_dp_connect with the gathered

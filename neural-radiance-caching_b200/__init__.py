@@ -38,6 +38,7 @@ ABI_SYMBOLS = [
     "nrc_b200_accumulate_render_radiance", "nrc_b200_propagate_train_radiance", "nrc_b200_permutation",
     "nrc_b200_permute_train_data", "nrc_b200_train_shuffled", "nrc_b200_train_batches", "nrc_b200_adjust_tile_size", "nrc_b200_update",
     "nrc_b200_debug_l2_read_bandwidth", "nrc_b200_release", "nrc_b200_set_accumulator", "nrc_b200_dp_connect_local", "nrc_b200_permute_train_data_with",
+    "nrc_b200_train_grad_noalloc", "nrc_b200_noalloc_limits",
 ]
 ACC_FP32, ACC_FP16 = 0, 1         # nrc_b200_set_accumulator
 
@@ -94,6 +95,9 @@ def lib():
         L.nrc_b200_last_loss_device.argtypes = [vp, P(vp)]
         L.nrc_b200_train_grad.argtypes = [vp, vp, vp, u32, u32, P(vp), vp]
         L.nrc_b200_train_apply.argtypes = [vp, vp, P(f32)]
+        if hasattr(L, "nrc_b200_train_grad_noalloc"):   # absent only from older A/B builds selected with NRC_B200_LIB
+            L.nrc_b200_train_grad_noalloc.argtypes = [vp, vp, vp, u32, u32, vp, vp, vp]
+            L.nrc_b200_noalloc_limits.argtypes = [P(u32), P(ctypes.c_uint64)]
         L.nrc_b200_n_params.argtypes = [vp, P(u32), P(u32)]
         L.nrc_b200_get_params.argtypes = [vp, i32, vp]
         L.nrc_b200_set_params.argtypes = [vp, i32, vp]
@@ -276,6 +280,12 @@ class Network:
                                          ctypes.byref(g), _ptr(stream)))
         return g.value
 
+    def train_grad_noalloc(self, inputs_d, targets_d, n_local, n_global, grad_out_d, loss_out_d=None, stream=None):
+        """train_grad with its scratch in the library's static device array: allocates nothing; the fp32 gradient (n_params
+        floats) and the loss go to caller buffers.  n_local <= noalloc_limits()[0].  No counterpart in the reference."""
+        _check(lib().nrc_b200_train_grad_noalloc(self._h, _ptr(inputs_d), _ptr(targets_d), int(n_local), int(n_global),
+                                                 _ptr(grad_out_d), _ptr(loss_out_d), _ptr(stream)))
+
     def train_apply(self, stream=None, want_loss=False):
         loss = ctypes.c_float()
         ran = _check(lib().nrc_b200_train_apply(self._h, _ptr(stream), ctypes.byref(loss) if want_loss else None))
@@ -360,3 +370,10 @@ class Network:
         c = ctypes.c_uint64()
         _check(lib().nrc_b200_launch_count(self._h, ctypes.byref(c)))
         return c.value
+
+
+def noalloc_limits():
+    """(max samples per nrc_b200_train_grad_noalloc call, bytes of the static device scratch every GPU holds)."""
+    n, b = ctypes.c_uint32(), ctypes.c_uint64()
+    _check(lib().nrc_b200_noalloc_limits(ctypes.byref(n), ctypes.byref(b)))
+    return n.value, b.value

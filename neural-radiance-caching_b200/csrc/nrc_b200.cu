@@ -818,3 +818,6 @@ int nrc_b200_last_loss_device(nrc_b200_handle h, const float** loss_d) {
     *loss_d = h->loss_d;
     return NRC_B200_OK;
 }
+
+#include <mutex>
+#include "nrc_noalloc.inc"   // nrc_b200_train_grad_noalloc: static device scratch, no allocation
