@@ -258,15 +258,47 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
 // one everybody polls.  All counters only ever increase (a barrier instance adds kBarrierFan to every group counter and
 // n_groups to the top one), so nothing is reset.  Ordering: acq_rel on the group counter chains the releases of the group
 // into the last arriver, whose release on the top counter publishes all of them to the acquiring pollers.
-__device__ __forceinline__ void grid_arrive(const TrainArgs& a, uint32_t tile) {
+#ifndef NRCB_BARRIER_FLAGS
+#define NRCB_BARRIER_FLAGS 0   // 0: one arrival counter (default); 1: one flag word per CTA, no atomics -- measured 3x SLOWER
+#endif                         // (barrier 2.0 -> 6.8 us: every thread of every CTA spinning on ld.acquire.gpu; profiles/r02b_experiments.md)
+// `target` = the value the arrival counter has once every CTA reached this barrier instance (monotonic over the handle's
+// life; the host advances it by the number of CTAs per instance).
+// Flag form (A/B build `barflags`): CTA `tile` publishes flag[tile] = target with ONE release store (nothing serialises in the L2 atomic unit: 128
+// same-address reds cost ~27 cycles each) and the waiters read all flags in parallel, one flag per thread -- still a single L2
+// round trip, unlike the two-level tree.  Flags live behind the counter (words 32 ..), values only ever increase.
+__device__ __forceinline__ void grid_arrive(const TrainArgs& a, uint32_t tile, uint32_t target) {
 #if NRCB_BARRIER_TREE
     uint32_t* sub = a.barrier_counter + 32u * (1u + tile / kBarrierFan);      // 128 bytes apart: separate L2 lines
     uint32_t old;
     asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(sub) : "memory");
     if ((old + 1u) % kBarrierFan == 0u)
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
+#elif NRCB_BARRIER_FLAGS
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(a.barrier_counter + 32u + tile), "r"(target) : "memory");
 #else
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(a.barrier_counter) : "memory");
+#endif
+}
+// Called by `stride` threads with idx = 0 .. stride-1 (a warp or the whole CTA); returns once every CTA has arrived.  The
+// caller synchronises its threads afterwards (bar.sync / __syncwarp), which extends the acquire to all of them.
+__device__ __forceinline__ void grid_wait(const TrainArgs& a, uint32_t target, uint32_t n_ctas, uint32_t idx, uint32_t stride) {
+#if NRCB_BARRIER_FLAGS && !NRCB_BARRIER_TREE
+    for (uint32_t t = idx; t < n_ctas; t += stride) {
+        const uint32_t* f = a.barrier_counter + 32u + t;
+        uint32_t seen, spins = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+            if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+        } while ((int32_t)(seen - target) < 0);
+    }
+#else
+    if (idx == 0) {
+        uint32_t seen, spins = 0;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
+            if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
+        } while ((int32_t)(seen - target) < 0);
+    }
 #endif
 }
 
@@ -339,22 +371,22 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         mbar_arrive_expect_tx(in_full, 7680);
         bulk_g2s(smem + L::kIn, a.in + (size_t)first * 15, 7680, in_full);
     }
-    if (tid == kWorkerWarps * 32 && has_tile) {
+    if (warp == kWorkerWarps && has_tile) {
         if (s > 0) {
-            if (kOverlapBarrier) {
-                uint32_t seen, spins = 0;
-                do {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
-                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-                } while ((int32_t)(seen - (a.barrier_target + (2 * (s - 1) + 1) * n_arrivals)) < 0);
+            if (kOverlapBarrier) {      // the whole issuer warp polls (one flag per lane and round)
+                grid_wait(a, a.barrier_target + (2 * (s - 1) + 1) * n_arrivals, n_tiles, lane, 32);
                 __threadfence();
+                __syncwarp();
             }
             // the weight image was rewritten with generic stores by every CTA in the previous step; the grid barrier
             // ordered them, this makes them visible to the bulk copy (async proxy).
-            asm volatile("fence.proxy.async;" ::: "memory");
+            if (lane == 0) asm volatile("fence.proxy.async;" ::: "memory");
         }
-        mbar_arrive_expect_tx(w_full, L::kWbytes);
-        bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
+        if (lane == 0) {
+            mbar_arrive_expect_tx(w_full, L::kWbytes);
+            bulk_g2s(smem + L::kW, a.params_img, L::kWbytes, w_full);
+        }
+        __syncwarp();
     }
 
     if (!has_tile) {
@@ -833,7 +865,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     tc_fence_before();
     __syncthreads();
     if (tid == 0) {
-        grid_arrive(a, tile);
+        grid_arrive(a, tile, a.barrier_target + 2 * s * n_arrivals);
         for (int i = 0; i < 8; ++i) s_lvmax[i] = 0;     // the scatter of this step is over: ready for the next step's maxima
     }
     // slice `tile` of the parameters belongs to this CTA in phase 3: at most one matrix parameter per thread.  Its optimizer
@@ -843,13 +875,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const bool pre_ok = a.apply && hi - lo <= (uint32_t)kTrainThreads;
     ParamState pst = {};
     if (pre_ok && (uint32_t)tid < hi - lo) pst = load_param_state(a, lo + tid);
-    if (tid == 0) {
-        uint32_t seen, spins = 0;
-        do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
-            if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-        } while ((int32_t)(seen - (a.barrier_target + 2 * s * n_arrivals)) < 0);
-    }
+    grid_wait(a, a.barrier_target + 2 * s * n_arrivals, n_tiles, tid, kTrainThreads);
     __syncthreads();
     tc_fence_after();
     stamp(5);
@@ -1030,16 +1056,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         __threadfence();
         fence_proxy_async_smem();
         __syncthreads();
-        if (tid == 0) {
-            grid_arrive(a, tile);
-            if (!(kOverlapBarrier && has_tile)) {   // otherwise the issuer warp completes the wait after the next encode has started
-                uint32_t seen, spins = 0;
-                do {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.barrier_counter) : "memory");
-                    if (++spins > NRCB_SPIN_LIMIT) asm volatile("trap;");
-                } while ((int32_t)(seen - (a.barrier_target + (2 * s + 1) * n_arrivals)) < 0);
-                __threadfence();
-            }
+        if (tid == 0) grid_arrive(a, tile, a.barrier_target + (2 * s + 1) * n_arrivals);
+        if (!(kOverlapBarrier && has_tile)) {   // otherwise the issuer warp completes the wait after the next encode has started
+            grid_wait(a, a.barrier_target + (2 * s + 1) * n_arrivals, n_tiles, tid, kTrainThreads);
+            __threadfence();
         }
         __syncthreads();
     }
