@@ -681,7 +681,9 @@ uint32_t nrc_b200_permutation(uint32_t i, uint32_t seed) { return permute16(i & 
 // launch gaps: 90 vs 76 us per step measured).
 static int train_steps(Net* h, const float* q, const float* t, int n_batches, uint32_t perm_n, uint32_t perm_seed) {
     const uint32_t n_global = global_batch(h, NRC_B200_BATCH_SIZE);
-    if (h->encoding == NRC_B200_HASH) {
+    // Hash: NRC_B200_HASH_MULTI=0 falls back to one launch per batch (the round-1 form, kept for A/B measurements)
+    static const bool hash_multi = [] { const char* e = getenv("NRC_B200_HASH_MULTI"); return !(e && e[0] == '0'); }();
+    if (h->encoding == NRC_B200_HASH && !hash_multi) {
         for (int b = 0; b < n_batches; ++b) {
             TrainArgs a = perm_n ? train_args(h, q, t, NRC_B200_BATCH_SIZE, n_global, 1)
                                  : train_args(h, q + (size_t)b * NRC_B200_BATCH_SIZE * 15, t + (size_t)b * NRC_B200_BATCH_SIZE * 3,
