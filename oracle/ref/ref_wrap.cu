@@ -56,7 +56,7 @@ int nrc_ref_get_params(void* h, int which, void* dst_h) {
     })
 }
 // sets fp32 master + fp16 training weights (Trainer::set_params_full_precision, which also writes the fp16 copy through
-// m_params_inference, i.e. the EMA buffer the network infers with, trainer.h:95-121); the Adam moments are left as they are
+// m_params_inference, i.e. the EMA buffer the network infers with, trainer.h:242-254); the Adam moments are left as they are
 // (fresh model => zeros).  The EMA filter itself starts from debias_old = 0 at step 1, so its first output does not depend on
 // what the buffer held.
 int nrc_ref_set_master(void* h, const float* src_h) {
