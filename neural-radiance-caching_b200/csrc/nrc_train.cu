@@ -24,6 +24,18 @@
 #include "nrc_encode.cuh"
 #include "nrc_frame.cuh"
 
+#ifndef NRCB_TIMING_SKIP_WGRAD
+#define NRCB_TIMING_SKIP_WGRAD 0
+#endif
+#ifndef NRCB_TIMING_SKIP_DUMP
+#define NRCB_TIMING_SKIP_DUMP 0
+#endif
+#ifndef NRCB_TIMING_SKIP_FINE
+#define NRCB_TIMING_SKIP_FINE 0
+#endif
+#ifndef NRCB_TIMING_SKIP_COARSE
+#define NRCB_TIMING_SKIP_COARSE 0
+#endif
 namespace nrcb {
 
 constexpr int kTT = 128;             // samples per tile
@@ -88,6 +100,9 @@ __device__ __forceinline__ void mma_dgrad(uint32_t d, uint32_t a_img, uint32_t w
 }
 // D[64 x n] = Dl^T[64 x 128] * Act[128 x n]         (both images read MN-major, K = 128 samples)
 __device__ __forceinline__ void mma_wgrad(uint32_t d, uint32_t delta_img, uint32_t act_img, int n) {
+#if NRCB_TIMING_SKIP_WGRAD      // timing experiment only (wrong gradients): what the weight-gradient MMAs cost the backward chain
+    return;
+#endif
     const uint32_t idesc = umma_idesc_f16(64, n, 1, 1);
 #pragma unroll
     for (int k = 0; k < 8; ++k)
@@ -594,8 +609,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 *reinterpret_cast<uint4*>(row_chunk(dbuf, row, hf * 4 + c)) = make_uint4(w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
             signal();
             // the commit just waited for covers the weight-gradient MMAs issued before it: dW_out (l = 3), dW_h(l+2) (l <= 2)
+#if !NRCB_TIMING_SKIP_DUMP    // timing experiment only: what the in-chain dumps cost
             if (l == 3) dump_out();
             else if (l <= 2) dump_hidden(l + 1);
+#endif
         }
         // all MMAs done: the remaining weight-gradient accumulators (and, Hash, dL/d(grid features)) are in TMEM
         wait_mma();
@@ -649,6 +666,12 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                 tmem_wait_ld();
                 const float g0 = grad_of(gw[0]), g1 = grad_of(gw[1]);
                 if (g0 == 0.0f && g1 == 0.0f) continue;
+#if NRCB_TIMING_SKIP_FINE       // timing experiments only (wrong gradients): scatter without its fine / coarse levels
+                if (lv >= kAgg) continue;
+#endif
+#if NRCB_TIMING_SKIP_COARSE
+                if (lv < kAgg) continue;
+#endif
                 const bool agg_level = lv < kAgg && !g16;
                 const uint32_t size = gm.offset[lv + 1] - gm.offset[lv], sy = gm.stride_y[lv], sz = gm.stride_z[lv];
                 const bool dense = (gm.dense_mask >> lv) & 1;
