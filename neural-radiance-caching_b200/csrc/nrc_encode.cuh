@@ -497,19 +497,32 @@ __device__ __forceinline__ void encode_frequency_half(const float (&q)[15], uint
 // pipelined gather (plain loads) and a part of the cheap features.  Output: four 16-byte chunks of the K-major feature row,
 // chunk ids in `ids` (chunk c = features 8c .. 8c+7: grid levels 4c .. 4c+3 for c < 4, one-blob pairs for c = 4..6, albedos + pad 7).
 //   HF0: chunks 0, 1 (levels 0..7), 4, 5 (one-blob of dims 0..3)      HF1: chunks 2, 3 (levels 8..15), 6 (dims 4, 5), 7
-template <int L0, int L>
-__device__ __forceinline__ void hash_half_levels(GridFetch (&F)[2], uint32_t (&e)[16], const float (&q)[15], const __half2* grid, const GridMeta& gm) {
+#ifndef NRCB_HASH_TRAIN_DEPTH
+#define NRCB_HASH_TRAIN_DEPTH 2     // levels of gathers in flight per thread in the training encode; 4 and 8 measured: no change (6.1 / 6.3 / 6.6 us:
+                                    // the encode is bound by L2 -> SM sector traffic with a cold L1, not by the load latency chain) and more registers
+#endif
+template <int L0, int L, int D>
+__device__ __forceinline__ void hash_half_levels(GridFetch (&F)[D], uint32_t (&e)[16], const float (&q)[15], const __half2* grid, const GridMeta& gm) {
     if constexpr (L < L0 + 8) {
-        if constexpr (L + 1 < L0 + 8) grid_issue_level<L + 1, false, false>(F[(L + 1) & 1], q, grid, 0u, gm);
-        e[L - L0] = grid_consume(F[L & 1]);
-        hash_half_levels<L0, L + 1>(F, e, q, grid, gm);
+        if constexpr (L + D - 1 < L0 + 8) grid_issue_level<L + D - 1, false, false>(F[(L + D - 1) % D], q, grid, 0u, gm);
+        e[L - L0] = grid_consume(F[L % D]);
+        hash_half_levels<L0, L + 1, D>(F, e, q, grid, gm);
+    }
+}
+template <int L0, int L, int D>
+__device__ __forceinline__ void hash_half_prologue(GridFetch (&F)[D], const float (&q)[15], const __half2* grid, const GridMeta& gm) {
+    if constexpr (L < L0 + D - 1) {
+        grid_issue_level<L, false, false>(F[L % D], q, grid, 0u, gm);
+        hash_half_prologue<L0, L + 1, D>(F, q, grid, gm);
     }
 }
 template <int HF>
 __device__ __forceinline__ void encode_hash_split(const float (&q)[15], const __half2* grid, const GridMeta& gm, uint32_t (&e)[16], int (&ids)[4]) {
-    GridFetch F[2];
-    grid_issue_level<8 * HF, false, false>(F[0], q, grid, 0u, gm);
-    hash_half_levels<8 * HF, 8 * HF>(F, e, q, grid, gm);
+    constexpr int D = NRCB_HASH_TRAIN_DEPTH;
+    static_assert(D >= 2 && D <= 8, "levels in flight");
+    GridFetch F[D];
+    hash_half_prologue<8 * HF, 8 * HF, D>(F, q, grid, gm);
+    hash_half_levels<8 * HF, 8 * HF, D>(F, e, q, grid, gm);
     if constexpr (HF == 0) {
         ids[0] = 0; ids[1] = 1; ids[2] = 4; ids[3] = 5;
         oneblob_pair<false>(q[3], q[4], e + 8);
