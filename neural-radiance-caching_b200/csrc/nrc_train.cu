@@ -30,6 +30,9 @@
 #ifndef NRCB_TIMING_SKIP_DUMP
 #define NRCB_TIMING_SKIP_DUMP 0
 #endif
+#ifndef NRCB_TIMING_ADAM_FEWER_WRITES
+#define NRCB_TIMING_ADAM_FEWER_WRITES 0
+#endif
 #ifndef NRCB_TIMING_ONLY_LEVEL
 #define NRCB_TIMING_ONLY_LEVEL -1
 #endif
@@ -185,6 +188,7 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
     if (is_matrix) a.ema_img[img_index(i, E)] = __float2half_rn(filtered);
 }
 
+constexpr uint32_t kLrTab = 64;   // entries of the per-step learning-rate table (grid_adam_chunk)
 #ifndef NRCB_ADAM_GROUPS
 #define NRCB_ADAM_GROUPS 2      // 4 measured slower (15.4 vs 13.7 us, longer tail over the CTAs)
 #endif
@@ -192,14 +196,14 @@ __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, f
 // in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
 // load_g(j) returns the reduced fp32 gradient of grid parameters j..j+3; clear: zero the scatter accumulator behind it.
 template <class LoadG, class ClearG>
-__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s,
+__device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s, const float* lr_tab,
                                                 LoadG load_g, ClearG clear_g) {
-    // The bias-corrected learning rate depends on the parameter's own step count only; almost every touched entry has
-    // been touched in every step so far, so the two powf of that common count are evaluated once per thread.
-    // (evaluated after the first group of loads has been issued, so it overlaps their latency)
+    // The bias-corrected learning rate depends on the parameter's own step count `cur` only (adam.h:106), which is the step
+    // number `common` of this launch minus the steps whose batch missed the entry.  lr_tab[d] (shared memory, filled once per
+    // step by the CTA with the same expression) holds lr(common - d) for d < kLrTab: the two powf per parameter are left to
+    // entries that were missed more often than that.  (A batch misses ~2 % of the hashed entries, so after a few steps some
+    // lane of practically every warp needed the powf pair: ~4 us of the 12 us this phase took.)
     const uint32_t common = a.opt_step + s;
-    float lr_common = 0.0f;
-    bool have_lr = false;
     constexpr int kG = NRCB_ADAM_GROUPS;   // float4 groups of one thread in flight: 7 vector loads each (one L2 round trip for all)
     for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 4 * kG * kTrainThreads) {
         float4 g[kG], w[kG], m1[kG], m2[kG];
@@ -221,10 +225,6 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                 pr[u] = *reinterpret_cast<const uint2*>(a.params + i);
             }
         }
-        if (!have_lr) {
-            lr_common = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)common)) / (1.0f - powf(a.beta1, (float)common)));
-            have_lr = true;
-        }
 #pragma unroll
         for (int u = 0; u < kG; ++u) {
             if (!live[u]) continue;
@@ -245,8 +245,9 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                     av[c] = a.beta1 * av[c] + (1.0f - a.beta1) * gradient;
                     bv[c] = a.beta2 * bv[c] + (1.0f - a.beta2) * (gradient * gradient);
                     const uint32_t cur = ++sv[c];
-                    const float lr = cur == common ? lr_common
-                                                   : a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+                    const uint32_t missed = common - cur;
+                    const float lr = missed < kLrTab ? lr_tab[missed]
+                                                     : a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
                     const float eff = fminf(fmaxf(lr / (sqrtf(bv[c]) + a.eps), 0.0f), 3.402823466e+38f);
                     wv[c] = wv[c] - eff * av[c];
                     pv[c] = __float2half_rn(wv[c]);
@@ -255,8 +256,10 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
                                         __half2float(pv[c]) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
                 ev[c] = __float2half_rn(filtered);
             }
+#if !NRCB_TIMING_ADAM_FEWER_WRITES   // timing experiment only: the optimizer pass without its two gradient copies (6 of 30 B written per parameter)
             *reinterpret_cast<float4*>(a.grad_f32 + i) = g[u];
             *reinterpret_cast<uint2*>(a.grads + i) = *reinterpret_cast<uint2*>(gh);
+#endif
             *reinterpret_cast<uint2*>(a.ema + i) = *reinterpret_cast<uint2*>(ev);
             if (any) {
                 *reinterpret_cast<float4*>(a.master + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
@@ -938,6 +941,13 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             }
             scratch[w] = acc;
         }
+        float* lr_tab = reinterpret_cast<float*>(smem + L::kScratch + 8192);      // behind the reduction scratch (<= 4.6 KB)
+        if constexpr (ENC == 1) {
+            if ((uint32_t)tid < kLrTab) {
+                const uint32_t common = a.opt_step + s, cur = common > (uint32_t)tid ? common - tid : 1u;
+                lr_tab[tid] = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+            }
+        }
         __syncthreads();
         const float* sc = reinterpret_cast<const float*>(scratch);
         auto slice_grad = [&](uint32_t j) {     // local gradient of parameter lo + j: groups summed in fixed order
@@ -971,7 +981,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     if (a.grid_grad_fp16) *reinterpret_cast<uint2*>(const_cast<__half*>(gg16) + j) = make_uint2(0u, 0u);
                     else *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 };
-                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, load_g, clear_g);
+                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, load_g, clear_g);
                 else
                     for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads)
                         a.grad_f32[NMLP + j] = a.grid_grad_fp16 ? __half2float(gg16[j]) : __ldcg(a.grid_grad + j);
@@ -1072,7 +1082,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     } while ((int32_t)(seen - seq) < 0 && !timed_out(spins, t0));
                 }
                 __syncthreads();
-                grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, [&](uint32_t j) {   // rank order: identical sums on every rank
+                grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, [&](uint32_t j) {   // rank order: identical sums on every rank
                     float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                     for (uint32_t r = 0; r < R; ++r) {
                         const float4 v = __ldcv(reinterpret_cast<const float4*>(row(me, r) + 2 * LLS + j));
