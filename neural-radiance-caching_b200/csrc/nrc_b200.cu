@@ -468,6 +468,11 @@ static TrainArgs train_args(Net* h, const float* q, const float* t, uint32_t n_l
     a.n_params = h->n_params; a.n_mlp = h->n_mlp;
     a.lr = h->lr; a.beta1 = h->beta1; a.beta2 = h->beta2; a.eps = h->eps; a.l2_reg = h->l2_reg;
     a.ema_decay = h->ema_decay; a.loss_scale = h->loss_scale;
+    {   // x / 2^k == x * 2^-k exactly (no denormals in reach: fp16 gradients, scale 128): the optimizer multiplies then
+        int ex = 0;
+        a.loss_scale_pow2 = (h->loss_scale > 0.0f && frexpf(h->loss_scale, &ex) == 0.5f) ? 1 : 0;
+        a.inv_loss_scale = 1.0f / h->loss_scale;
+    }
     // EmaOptimizer::step (ema.h:107-108): std::pow(float, unsigned) promotes to double
     a.n_steps = n_steps;
     for (uint32_t s = 0; s < n_steps && s < 4; ++s) {

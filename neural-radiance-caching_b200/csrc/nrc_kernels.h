@@ -48,6 +48,8 @@ struct TrainArgs {
     uint32_t barrier_target;         // value the top counter reaches when every CTA has arrived at the launch's FIRST barrier
     uint32_t n_params, n_mlp;
     float lr, beta1, beta2, eps, l2_reg, ema_decay, loss_scale;
+    float inv_loss_scale;            // 1 / loss_scale, used instead of the division when loss_scale is a power of two (exact)
+    int loss_scale_pow2;
     float ema_debias_old[4], ema_debias_new[4];   // per step of the launch
     int apply;
     int acc16;                       // forward / backward-chain MMAs with fp16 accumulators (the reference's wmma accumulator<__half>)

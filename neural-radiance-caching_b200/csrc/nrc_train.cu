@@ -60,7 +60,11 @@ struct TrainSmem {
     static constexpr int kIn = kG + 4096;                     // raw queries 7680 B
     static constexpr int kBar = kIn + 7680;
     static constexpr int kTotal = kBar + 128;
-    static constexpr int kScratch = kX;                       // phase 3 reuses the activation area
+    static constexpr int kScratch = kX;                       // phase 3 reuses the activation area: reduction scratch, lr table at + 8192
+    // Hash optimizer phase: the CTA's slice of the grid optimizer state, bulk-copied in while the grid barrier is pending.
+    static constexpr int kStage16 = kW;                       // [params | ema]            2 x n x 2 B  (the weight image is dead by then)
+    static constexpr int kStage32 = kX + 8192 + 256;          // [master | m1 | m2 | steps] 4 x n x 4 B  (behind scratch + lr table)
+    static constexpr int kStageMax = ((kBar - kStage32) / 16 < kWbytes / 4 ? (kBar - kStage32) / 16 : kWbytes / 4) & ~7;   // parameters
 };
 
 // TMEM columns
@@ -156,59 +160,110 @@ __device__ __forceinline__ void adam_ema_matrix_param(const TrainArgs& a, uint32
     a.ema_img[img] = e_half;        // the query kernel bulk-copies this image instead of re-formatting the weights per CTA
 }
 
+// ---------------------------------------------------------------- optimizer: ONE grid parameter, in registers
+// adam_step for a parameter without weight decay (adam.h:75-118: skipped entirely when its gradient is zero) followed by
+// ema_step_half_precision (ema.h:62-76).  Branch-free on purpose: the update is always evaluated and SELECTED by `nz`, so the
+// compiler interleaves the independent chains of the parameters a thread holds (with a branch per parameter the IEEE division /
+// square-root sequences ran one after the other: ~165 instructions per parameter on 9 warps per SM were the 12 us of this phase).
+// Every product and sum is an explicit round-to-nearest intrinsic: the fused step kernel (both forms of its grid pass) and the
+// stand-alone optimizer kernel of the NCCL path round identically whatever the compiler would contract.
+// lr_tab (may be null): lr(common - d) for d < kLrTab, see grid_adam4.
+constexpr uint32_t kLrTab = 64;   // entries of the per-step learning-rate table
+__device__ __forceinline__ float adam_bias_corrected_lr(const TrainArgs& a, uint32_t cur) {
+    return a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+}
+__device__ __forceinline__ bool grid_param_update(const TrainArgs& a, float g32, uint32_t common, uint32_t s, const float* lr_tab,
+                                                  float& w, float& m1, float& m2, uint32_t& st, __half& p, __half& e, __half& gh) {
+    gh = __float2half_rn(g32);            // the reference's gradient buffer is fp16 (trainer.h:322-336)
+    const float gf = __half2float(gh);
+    const float gradient = a.loss_scale_pow2 ? __fmul_rn(gf, a.inv_loss_scale) : __fdiv_rn(gf, a.loss_scale);
+    const bool nz = gradient != 0.0f;
+    const float n1 = fmaf(a.beta1, m1, __fmul_rn(1.0f - a.beta1, gradient));
+    const float n2 = fmaf(a.beta2, m2, __fmul_rn(1.0f - a.beta2, __fmul_rn(gradient, gradient)));
+    const uint32_t cur = st + 1, missed = common - cur;
+    float lr;
+    if (lr_tab != nullptr && (missed < kLrTab || !nz)) lr = lr_tab[min(missed, kLrTab - 1)];   // (unused when !nz)
+    else lr = adam_bias_corrected_lr(a, cur);
+    const float eff = fminf(fmaxf(__fdiv_rn(lr, __fadd_rn(__fsqrt_rn(n2), a.eps)), 0.0f), 3.402823466e+38f);
+    const float nw = fmaf(-eff, n1, w);
+    m1 = nz ? n1 : m1;
+    m2 = nz ? n2 : m2;
+    st = nz ? cur : st;
+    w = nz ? nw : w;
+    p = nz ? __float2half_rn(nw) : p;
+    const float old_part = __fmul_rn(__fmul_rn(__half2float(e), a.ema_decay), a.ema_debias_old[s]);
+    e = __float2half_rn(__fmul_rn(fmaf(__half2float(p), 1.0f - a.ema_decay, old_part), a.ema_debias_new[s]));
+    return nz;
+}
+
 // ---------------------------------------------------------------- optimizer (per parameter)
 // adam_step (tcnn/optimizers/adam.h:75-118) followed by ema_step_half_precision (ema.h:62-76).  `g32` is the
 // reduced fp32 gradient (loss-scaled); the reference's gradient buffer is fp16 (trainer.h:322-336), so it is
 // rounded to fp16 first.  Also maintains the UMMA image of the fp16 training weights.
 __device__ __forceinline__ void adam_ema_param(const TrainArgs& a, uint32_t i, float g32, uint32_t E, uint32_t s = 0) {
     if (i < a.n_mlp) { adam_ema_matrix_param(a, i, g32, E, s, load_param_state(a, i)); return; }
-    const __half gh = __float2half_rn(g32);
+    float w = a.master[i], m1 = a.m1[i], m2 = a.m2[i];
+    uint32_t st = a.steps[i];
+    __half p = a.params[i], e = a.ema[i], gh;
+    const bool nz = grid_param_update(a, g32, a.opt_step + s, s, nullptr, w, m1, m2, st, p, e, gh);
     a.grads[i] = gh;
-    float gradient = __half2float(gh) / a.loss_scale;
-    const bool is_matrix = i < a.n_mlp;
-    __half w_half = a.params[i];
-    if (is_matrix || gradient != 0.0f) {   // grid parameters without gradient are skipped entirely (adam.h:80-82)
-        const float weight_fp = a.master[i];
-        if (is_matrix) gradient += a.l2_reg * weight_fp;
-        const float gradient_sq = gradient * gradient;
-        const float m1 = a.m1[i] = a.beta1 * a.m1[i] + (1.0f - a.beta1) * gradient;
-        const float m2 = a.m2[i] = a.beta2 * a.m2[i] + (1.0f - a.beta2) * gradient_sq;
-        const uint32_t cur = ++a.steps[i];
-        const float lr = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
-        const float eff = fminf(fmaxf(lr / (sqrtf(m2) + a.eps), 0.0f), 3.402823466e+38f);
-        const float new_weight = weight_fp - eff * m1;
-        a.master[i] = new_weight;
-        w_half = __float2half_rn(new_weight);
-        a.params[i] = w_half;
-        if (is_matrix) a.params_img[img_index(i, E)] = w_half;
-    }
-    const float filtered = (__half2float(a.ema[i]) * a.ema_decay * a.ema_debias_old[s] +
-                            __half2float(w_half) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
-    a.ema[i] = __float2half_rn(filtered);
-    if (is_matrix) a.ema_img[img_index(i, E)] = __float2half_rn(filtered);
+    a.ema[i] = e;
+    if (nz) { a.master[i] = w; a.m1[i] = m1; a.m2[i] = m2; a.steps[i] = st; a.params[i] = p; }
 }
 
-constexpr uint32_t kLrTab = 64;   // entries of the per-step learning-rate table (grid_adam_chunk)
+#ifndef NRCB_ADAM_STAGED
+#define NRCB_ADAM_STAGED 0     // 1: Hash optimizer state of the CTA's slice staged in shared memory during the grid-barrier wait -- measured
+                               // SLOWER (12.5 -> 13.2 us: the pass is bound by its arithmetic, not by its loads) and it makes the four-step kernel spill
+#endif
 #ifndef NRCB_ADAM_GROUPS
 #define NRCB_ADAM_GROUPS 2      // 4 measured slower (15.4 vs 13.7 us, longer tail over the CTAs)
 #endif
 // Adam + EMA over grid parameters [glo, ghi) (multiples of 4) of one CTA, four parameters per thread and NRCB_ADAM_GROUPS groups
 // in flight: the per-parameter version walked a dependent chain of ~7 L2 round trips per parameter (46 us measured).
 // load_g(j) returns the reduced fp32 gradient of grid parameters j..j+3; clear: zero the scatter accumulator behind it.
+// Adam + EMA for four consecutive grid parameters i .. i+3 (= grid parameters j .. j+3) whose gradient and state are in registers;
+// writes the new state.  Shared by the two forms of the optimizer pass below, so that they round identically.
+// The bias-corrected learning rate depends on the parameter's own step count `cur` only (adam.h:106), which is the step number
+// `common` of this launch minus the steps whose batch missed the entry.  lr_tab[d] (shared memory, filled once per step by the CTA
+// with the same expression) holds lr(common - d) for d < kLrTab: the two powf per parameter are left to entries that were missed
+// more often than that.  (A batch misses ~2 % of the hashed entries, so after a few steps some lane of practically every warp
+// needed the powf pair: ~4 us of the 16 us this phase took.)
+struct GridState4 { float4 w, m1, m2; uint4 st; uint2 em, pr; };
+template <class ClearG>
+__device__ __forceinline__ void grid_adam4(const TrainArgs& a, uint32_t i, uint32_t j, const float4& g, const GridState4& v, uint32_t common, uint32_t s,
+                                           const float* lr_tab, ClearG clear_g) {
+    float gv[4] = {g.x, g.y, g.z, g.w}, wv[4] = {v.w.x, v.w.y, v.w.z, v.w.w};
+    float av[4] = {v.m1.x, v.m1.y, v.m1.z, v.m1.w}, bv[4] = {v.m2.x, v.m2.y, v.m2.z, v.m2.w};
+    uint32_t sv[4] = {v.st.x, v.st.y, v.st.z, v.st.w};
+    __half ev[4], pv[4], gh[4];
+    *reinterpret_cast<uint2*>(ev) = v.em;
+    *reinterpret_cast<uint2*>(pv) = v.pr;
+    bool any = false;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) any |= grid_param_update(a, gv[c], common, s, lr_tab, wv[c], av[c], bv[c], sv[c], pv[c], ev[c], gh[c]);
+#if !NRCB_TIMING_ADAM_FEWER_WRITES   // timing experiment only: the optimizer pass without its two gradient copies (6 of 30 B written per parameter)
+    *reinterpret_cast<float4*>(a.grad_f32 + i) = g;
+    *reinterpret_cast<uint2*>(a.grads + i) = *reinterpret_cast<uint2*>(gh);
+#endif
+    *reinterpret_cast<uint2*>(a.ema + i) = *reinterpret_cast<uint2*>(ev);
+    if (any) {
+        *reinterpret_cast<float4*>(a.master + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
+        *reinterpret_cast<float4*>(a.m1 + i) = make_float4(av[0], av[1], av[2], av[3]);
+        *reinterpret_cast<float4*>(a.m2 + i) = make_float4(bv[0], bv[1], bv[2], bv[3]);
+        *reinterpret_cast<uint4*>(a.steps + i) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
+        *reinterpret_cast<uint2*>(a.params + i) = *reinterpret_cast<uint2*>(pv);
+    }
+    if (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f) clear_g(j);   // also gradients that round to 0 in fp16
+}
+// Form 1 (any slice size): state and gradient from global memory, NRCB_ADAM_GROUPS groups in flight per thread.
 template <class LoadG, class ClearG>
 __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t E, uint32_t s, const float* lr_tab,
                                                 LoadG load_g, ClearG clear_g) {
-    // The bias-corrected learning rate depends on the parameter's own step count `cur` only (adam.h:106), which is the step
-    // number `common` of this launch minus the steps whose batch missed the entry.  lr_tab[d] (shared memory, filled once per
-    // step by the CTA with the same expression) holds lr(common - d) for d < kLrTab: the two powf per parameter are left to
-    // entries that were missed more often than that.  (A batch misses ~2 % of the hashed entries, so after a few steps some
-    // lane of practically every warp needed the powf pair: ~4 us of the 12 us this phase took.)
     const uint32_t common = a.opt_step + s;
     constexpr int kG = NRCB_ADAM_GROUPS;   // float4 groups of one thread in flight: 7 vector loads each (one L2 round trip for all)
     for (uint32_t j0 = glo + 4 * tid; j0 < ghi; j0 += 4 * kG * kTrainThreads) {
-        float4 g[kG], w[kG], m1[kG], m2[kG];
-        uint4 st[kG];
-        uint2 em[kG], pr[kG];
+        float4 g[kG];
+        GridState4 v[kG];
         bool live[kG];
 #pragma unroll
         for (int u = 0; u < kG; ++u) {
@@ -217,58 +272,51 @@ __device__ __forceinline__ void grid_adam_chunk(const TrainArgs& a, uint32_t bas
             if (live[u]) {
                 const uint32_t i = base + j;
                 g[u] = load_g(j);
-                w[u] = *reinterpret_cast<const float4*>(a.master + i);
-                m1[u] = *reinterpret_cast<const float4*>(a.m1 + i);
-                m2[u] = *reinterpret_cast<const float4*>(a.m2 + i);
-                st[u] = *reinterpret_cast<const uint4*>(a.steps + i);
-                em[u] = *reinterpret_cast<const uint2*>(a.ema + i);
-                pr[u] = *reinterpret_cast<const uint2*>(a.params + i);
+                v[u].w = *reinterpret_cast<const float4*>(a.master + i);
+                v[u].m1 = *reinterpret_cast<const float4*>(a.m1 + i);
+                v[u].m2 = *reinterpret_cast<const float4*>(a.m2 + i);
+                v[u].st = *reinterpret_cast<const uint4*>(a.steps + i);
+                v[u].em = *reinterpret_cast<const uint2*>(a.ema + i);
+                v[u].pr = *reinterpret_cast<const uint2*>(a.params + i);
             }
         }
 #pragma unroll
         for (int u = 0; u < kG; ++u) {
             if (!live[u]) continue;
-            const uint32_t j = j0 + u * 4 * kTrainThreads, i = base + j;
-            float gv[4] = {g[u].x, g[u].y, g[u].z, g[u].w}, wv[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
-            float av[4] = {m1[u].x, m1[u].y, m1[u].z, m1[u].w}, bv[4] = {m2[u].x, m2[u].y, m2[u].z, m2[u].w};
-            uint32_t sv[4] = {st[u].x, st[u].y, st[u].z, st[u].w};
-            __half ev[4], pv[4], gh[4];
-            *reinterpret_cast<uint2*>(ev) = em[u];
-            *reinterpret_cast<uint2*>(pv) = pr[u];
-            bool any = false;
+            const uint32_t j = j0 + u * 4 * kTrainThreads;
+            grid_adam4(a, base + j, j, g[u], v[u], common, s, lr_tab, clear_g);
+        }
+    }
+}
+// Form 2: the CTA's whole state slice (20 B per parameter) was bulk-copied into shared memory while the grid barrier was pending
+// (it does not depend on the gradient); after the barrier only the gradients come from L2 -- 4 B per parameter, the loads of
+// kStagedRounds rounds in flight at once -- and the state is read from shared memory.  Layout of the staging area: st32 =
+// [master | m1 | m2 | steps] (n x 4 B each), st16 = [params | ema] (n x 2 B each), n = ghi - glo.
+// kStagedRounds = rounds of 4 * kTrainThreads parameters whose gradient loads are in flight together (6 cover a CTA's slice of the
+// default table in one L2 round trip; the data-parallel load sums dp_world rows per group and uses 2).
+template <int kStagedRounds, class LoadG, class ClearG>
+__device__ __forceinline__ void grid_adam_staged(const TrainArgs& a, uint32_t base, uint32_t glo, uint32_t ghi, int tid, uint32_t s, const float* lr_tab,
+                                                 const uint8_t* st32, const uint8_t* st16, LoadG load_g, ClearG clear_g) {
+    const uint32_t common = a.opt_step + s, n = ghi - glo;
+    for (uint32_t r0 = 4 * tid; r0 < n; r0 += 4 * kStagedRounds * kTrainThreads) {
+        float4 g[kStagedRounds];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                gh[c] = __float2half_rn(gv[c]);
-                const float gradient = __half2float(gh[c]) / a.loss_scale;
-                if (gradient != 0.0f) {       // adam.h:80-82: grid parameters without gradient are skipped entirely
-                    any = true;
-                    av[c] = a.beta1 * av[c] + (1.0f - a.beta1) * gradient;
-                    bv[c] = a.beta2 * bv[c] + (1.0f - a.beta2) * (gradient * gradient);
-                    const uint32_t cur = ++sv[c];
-                    const uint32_t missed = common - cur;
-                    const float lr = missed < kLrTab ? lr_tab[missed]
-                                                     : a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
-                    const float eff = fminf(fmaxf(lr / (sqrtf(bv[c]) + a.eps), 0.0f), 3.402823466e+38f);
-                    wv[c] = wv[c] - eff * av[c];
-                    pv[c] = __float2half_rn(wv[c]);
-                }
-                const float filtered = (__half2float(ev[c]) * a.ema_decay * a.ema_debias_old[s] +
-                                        __half2float(pv[c]) * (1.0f - a.ema_decay)) * a.ema_debias_new[s];
-                ev[c] = __float2half_rn(filtered);
-            }
-#if !NRCB_TIMING_ADAM_FEWER_WRITES   // timing experiment only: the optimizer pass without its two gradient copies (6 of 30 B written per parameter)
-            *reinterpret_cast<float4*>(a.grad_f32 + i) = g[u];
-            *reinterpret_cast<uint2*>(a.grads + i) = *reinterpret_cast<uint2*>(gh);
-#endif
-            *reinterpret_cast<uint2*>(a.ema + i) = *reinterpret_cast<uint2*>(ev);
-            if (any) {
-                *reinterpret_cast<float4*>(a.master + i) = make_float4(wv[0], wv[1], wv[2], wv[3]);
-                *reinterpret_cast<float4*>(a.m1 + i) = make_float4(av[0], av[1], av[2], av[3]);
-                *reinterpret_cast<float4*>(a.m2 + i) = make_float4(bv[0], bv[1], bv[2], bv[3]);
-                *reinterpret_cast<uint4*>(a.steps + i) = make_uint4(sv[0], sv[1], sv[2], sv[3]);
-                *reinterpret_cast<uint2*>(a.params + i) = *reinterpret_cast<uint2*>(pv);
-            }
-            if (gv[0] != 0.0f || gv[1] != 0.0f || gv[2] != 0.0f || gv[3] != 0.0f) clear_g(j);   // also gradients that round to 0 in fp16
+        for (int u = 0; u < kStagedRounds; ++u) {
+            const uint32_t r = r0 + u * 4 * kTrainThreads;
+            if (r < n) g[u] = load_g(glo + r);
+        }
+#pragma unroll
+        for (int u = 0; u < kStagedRounds; ++u) {
+            const uint32_t r = r0 + u * 4 * kTrainThreads;
+            if (r >= n) continue;
+            GridState4 v;
+            v.w = *reinterpret_cast<const float4*>(st32 + (size_t)r * 4);
+            v.m1 = *reinterpret_cast<const float4*>(st32 + ((size_t)n + r) * 4);
+            v.m2 = *reinterpret_cast<const float4*>(st32 + ((size_t)2 * n + r) * 4);
+            v.st = *reinterpret_cast<const uint4*>(st32 + ((size_t)3 * n + r) * 4);
+            v.pr = *reinterpret_cast<const uint2*>(st16 + (size_t)r * 2);
+            v.em = *reinterpret_cast<const uint2*>(st16 + ((size_t)n + r) * 2);
+            grid_adam4(a, base + glo + r, glo + r, g[u], v, common, s, lr_tab, clear_g);
         }
     }
 }
@@ -354,6 +402,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     uint64_t* w_full = bars + 3;    // bulk copy of the weight image
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
     float* warp_loss = reinterpret_cast<float*>(bars + 5);   // [4]
+    uint64_t* st_full = bars + 7;   // bulk copy of the grid optimizer-state slice (Hash)
     uint32_t* s_lvmax = reinterpret_cast<uint32_t*>(bars + 8);   // [8] Hash scatter: per coarse level, tile maximum of |dL/dy| (float bits)
 
     const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;   // provably warp-uniform
@@ -368,7 +417,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     stamp(0);
 
     if (tid == 0) {
-        mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1);
+        mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1); mbar_init(st_full, 1);
         fence_mbar_init();
         for (int i = 0; i < 8; ++i) s_lvmax[i] = 0;
     }
@@ -901,6 +950,28 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     __threadfence();
     tc_fence_before();
     __syncthreads();
+    // this CTA's slice of the grid parameters in phase 3 (multiples of 8: 16-byte bulk copies of the fp16 arrays)
+    const uint32_t n_grid = a.n_params - NMLP;
+    const uint32_t SG = ((n_grid + n_tiles - 1) / n_tiles + 7) & ~7u;
+    const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
+    const bool staged = ENC == 1 && NRCB_ADAM_STAGED && a.apply && ghi > glo && ghi - glo <= (uint32_t)L::kStageMax;
+    if constexpr (ENC == 1) {
+        if (staged && tid == 32) {
+            // every buffer of phase 1 is dead (the __syncthreads above): the state slice lands in shared memory while the grid
+            // barrier is pending.  fence.proxy.async: generic accesses of the staging area (WAR) and the generic stores that
+            // wrote this state in the previous step precede the async-proxy copies.
+            const uint32_t n = ghi - glo;
+            const size_t i0 = (size_t)NMLP + glo;
+            asm volatile("fence.proxy.async;" ::: "memory");
+            mbar_arrive_expect_tx(st_full, n * 20);
+            bulk_g2s(smem + L::kStage32, a.master + i0, n * 4, st_full);
+            bulk_g2s(smem + L::kStage32 + (size_t)n * 4, a.m1 + i0, n * 4, st_full);
+            bulk_g2s(smem + L::kStage32 + (size_t)n * 8, a.m2 + i0, n * 4, st_full);
+            bulk_g2s(smem + L::kStage32 + (size_t)n * 12, a.steps + i0, n * 4, st_full);
+            bulk_g2s(smem + L::kStage16, a.params + i0, n * 2, st_full);
+            bulk_g2s(smem + L::kStage16 + (size_t)n * 2, a.ema + i0, n * 2, st_full);
+        }
+    }
     if (tid == 0) {
         grid_arrive(a, tile, a.barrier_target + 2 * s * n_arrivals);
         for (int i = 0; i < 8; ++i) s_lvmax[i] = 0;     // the scatter of this step is over: ready for the next step's maxima
@@ -945,7 +1016,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
         if constexpr (ENC == 1) {
             if ((uint32_t)tid < kLrTab) {
                 const uint32_t common = a.opt_step + s, cur = common > (uint32_t)tid ? common - tid : 1u;
-                lr_tab[tid] = a.lr * (sqrtf(1.0f - powf(a.beta2, (float)cur)) / (1.0f - powf(a.beta1, (float)cur)));
+                lr_tab[tid] = adam_bias_corrected_lr(a, cur);
             }
         }
         __syncthreads();
@@ -955,9 +1026,6 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             for (uint32_t g = 0; g < groups; ++g) gsum += sc[(g * ncol4 + (j >> 2)) * 4 + (j & 3)];
             return gsum;
         };
-        const uint32_t n_grid = a.n_params - NMLP;
-        const uint32_t SG = ((n_grid + n_tiles - 1) / n_tiles + 3) & ~3u;   // multiple of 4: float4 groups
-        const uint32_t glo = min(n_grid, tile * SG), ghi = min(n_grid, glo + SG);
         const uint32_t R = a.dp_world, me = a.dp_rank;
         if (!(a.apply && R > 1)) {
             // ---- single GPU (or gradient-only for an external all-reduce)
@@ -981,7 +1049,10 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     if (a.grid_grad_fp16) *reinterpret_cast<uint2*>(const_cast<__half*>(gg16) + j) = make_uint2(0u, 0u);
                     else *reinterpret_cast<float4*>(a.grid_grad + j) = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                 };
-                if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, load_g, clear_g);
+                if (staged) {
+                    mbar_wait(st_full, s & 1);
+                    grid_adam_staged<6>(a, NMLP, glo, ghi, tid, s, lr_tab, smem + L::kStage32, smem + L::kStage16, load_g, clear_g);
+                } else if (a.apply) grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, load_g, clear_g);
                 else
                     for (uint32_t j = glo + tid; j < ghi; j += kTrainThreads)
                         a.grad_f32[NMLP + j] = a.grid_grad_fp16 ? __half2float(gg16[j]) : __ldcg(a.grid_grad + j);
@@ -1082,14 +1153,18 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
                     } while ((int32_t)(seen - seq) < 0 && !timed_out(spins, t0));
                 }
                 __syncthreads();
-                grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, [&](uint32_t j) {   // rank order: identical sums on every rank
+                auto load_sum = [&](uint32_t j) {   // rank order: identical sums on every rank
                     float4 g = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
                     for (uint32_t r = 0; r < R; ++r) {
                         const float4 v = __ldcv(reinterpret_cast<const float4*>(row(me, r) + 2 * LLS + j));
                         g.x += v.x; g.y += v.y; g.z += v.z; g.w += v.w;
                     }
                     return g;
-                }, [](uint32_t) {});
+                };
+                if (staged) {
+                    mbar_wait(st_full, s & 1);
+                    grid_adam_staged<2>(a, NMLP, glo, ghi, tid, s, lr_tab, smem + L::kStage32, smem + L::kStage16, load_sum, [](uint32_t) {});
+                } else grid_adam_chunk(a, NMLP, glo, ghi, tid, E, s, lr_tab, load_sum, [](uint32_t) {});
             }
         }
     }
