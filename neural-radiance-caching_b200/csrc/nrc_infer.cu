@@ -213,9 +213,9 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 if (gtid == 0) {
                     const bool st = acc_staged(t);
                     mbar_arrive_expect_tx(&in_full[g], L::kStage + (st ? L::kAcc : 0));
-                    bulk_g2s(s_in, src, L::kStage, &in_full[g]);
+                    bulk_g2s_stream(s_in, src, L::kStage, &in_full[g]);
                     if (st) {
-                        bulk_g2s(s_acc + par * L::kAcc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &in_full[g]);
+                        bulk_g2s_stream(s_acc + par * L::kAcc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &in_full[g]);
                         bulk_g2s(s_acc + par * L::kAcc + kTile * 12, acc.out + (size_t)t * kTile, kTile * 16, &in_full[g]);
                     }
                 }
@@ -316,7 +316,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             if (out_vec_ok && rows == kTile) {
                 s_out[row * 3 + 0] = y[0]; s_out[row * 3 + 1] = y[1]; s_out[row * 3 + 2] = y[2];
                 bar_sync_id(bar_d);
-                if (gtid < 96) reinterpret_cast<float4*>(dst)[gtid] = reinterpret_cast<const float4*>(s_out)[gtid];
+                if (gtid < 96) st_stream_f4(reinterpret_cast<float4*>(dst) + gtid, reinterpret_cast<const float4*>(s_out)[gtid]);
             } else if (row < rows) {
                 dst[row * 3 + 0] = y[0]; dst[row * 3 + 1] = y[1]; dst[row * 3 + 2] = y[2];
             }
@@ -342,7 +342,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 if (in_bulk_ok && rows == kTile) {
                     if (gtid == 0) {
                         mbar_arrive_expect_tx(&in_full[g], L::kStage);
-                        bulk_g2s(s_in, src, L::kStage, &in_full[g]);
+                        bulk_g2s_stream(s_in, src, L::kStage, &in_full[g]);
                     }
                 } else {  // ragged tail / unaligned caller buffer: plain loads, zero-fill the missing rows
                     for (uint32_t i = gtid; i < kTile * 15; i += 128) s_in[i] = i < rows * 15 ? __ldg(src + i) : 0.0f;
@@ -374,7 +374,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 const bool st = acc_staged(t);
                 if (st && gtid == 0) {
                     mbar_arrive_expect_tx(&acc_full[g], L::kAcc);
-                    bulk_g2s(s_acc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &acc_full[g]);
+                    bulk_g2s_stream(s_acc, acc.throughput + (size_t)t * kTile * 3, kTile * 12, &acc_full[g]);
                     bulk_g2s(s_acc + kTile * 12, acc.out + (size_t)t * kTile, kTile * 16, &acc_full[g]);
                 }
                 hidden_epilogue();
