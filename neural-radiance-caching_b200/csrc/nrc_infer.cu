@@ -23,6 +23,9 @@
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
 
+#ifndef NRCB_TIMING_SKIP_ENCODE
+#define NRCB_TIMING_SKIP_ENCODE 0     // timing experiment only (wrong radiance): Frequency without the encode slices of the next tile, Hash without the gathers
+#endif
 namespace nrcb {
 
 #ifndef NRC_HASH_GATHER
@@ -378,11 +381,11 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                     bulk_g2s(s_acc + kTile * 12, acc.out + (size_t)t * kTile, kTile * 16, &acc_full[g]);
                 }
                 hidden_epilogue();
-                run_layer(std::integral_constant<int, 1>{}, [&] { if (has_next) encode_frequency_slice<0>(q, a_row); }); hidden_epilogue();
-                run_layer(std::integral_constant<int, 2>{}, [&] { if (has_next) encode_frequency_slice<1>(q, a_row); }); hidden_epilogue();
-                run_layer(std::integral_constant<int, 3>{}, [&] { if (has_next) encode_frequency_slice<2>(q, a_row); }); hidden_epilogue();
-                run_layer(std::integral_constant<int, 4>{}, [&] { if (has_next) encode_frequency_slice<3>(q, a_row); }); hidden_epilogue();
-                run_layer(std::integral_constant<int, 5>{}, [&] { if (has_next) encode_frequency_slice<4>(q, a_row); });
+                run_layer(std::integral_constant<int, 1>{}, [&] { if (has_next && !NRCB_TIMING_SKIP_ENCODE) encode_frequency_slice<0>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 2>{}, [&] { if (has_next && !NRCB_TIMING_SKIP_ENCODE) encode_frequency_slice<1>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 3>{}, [&] { if (has_next && !NRCB_TIMING_SKIP_ENCODE) encode_frequency_slice<2>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 4>{}, [&] { if (has_next && !NRCB_TIMING_SKIP_ENCODE) encode_frequency_slice<3>(q, a_row); }); hidden_epilogue();
+                run_layer(std::integral_constant<int, 5>{}, [&] { if (has_next && !NRCB_TIMING_SKIP_ENCODE) encode_frequency_slice<4>(q, a_row); });
                 if (st) { mbar_wait(&acc_full[g], ph_acc); ph_acc ^= 1; }
                 finish_tile(t, st ? s_acc : nullptr);
             }
@@ -417,6 +420,7 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
             // ---- encode -> A operand of the input layer (its previous contents were consumed long ago)
             if constexpr (ENC == 1 && NRC_HASH_GATHER != 0) {
                 if constexpr (NRC_HASH_DEPTH <= 2) {
+                    if (!NRCB_TIMING_SKIP_ENCODE)      // timing experiment only: the query kernel without its hash-grid gathers
                     encode_hash_grid_to_tmem(q, grid, smem_u32(smem + L::kL0Off), gm, tA);
                     encode_hash_rest_to_tmem(q, tA);
                 }
