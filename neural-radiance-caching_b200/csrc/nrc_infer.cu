@@ -23,6 +23,9 @@
 #include "nrc_kernels.h"
 #include "nrc_encode.cuh"
 
+#ifndef NRCB_INFER_DIRECT_WAIT
+#define NRCB_INFER_DIRECT_WAIT 0      // 1: every warp of a group waits on the commit mbarrier itself -- measured slower (164.3 vs 162.0 us, A/B build directwait)
+#endif
 #ifndef NRCB_TIMING_SKIP_ENCODE
 #define NRCB_TIMING_SKIP_ENCODE 0     // timing experiment only (wrong radiance): Frequency without the encode slices of the next tile, Hash without the gathers
 #endif
@@ -245,11 +248,20 @@ nrc_infer_kernel(const float* __restrict__ in, float* __restrict__ out, uint32_t
                 __syncwarp();
                 overlap();
                 mbar_wait(&d_ready[g], ph_d);
+#if !NRCB_INFER_DIRECT_WAIT
                 bar_sync_id(bar_d);
+#endif
             } else {
                 bar_arrive_id(bar_a);
                 overlap();
+#if NRCB_INFER_DIRECT_WAIT
+                // every warp of the group waits for the commit itself (the next commit cannot happen before all four warps have
+                // passed this wait and arrived at bar_a again, so no warp can miss a phase): one hop less than being released by
+                // the issuing warp through a second named barrier
+                mbar_wait(&d_ready[g], ph_d);
+#else
                 bar_sync_id(bar_d);
+#endif
             }
             ph_d ^= 1;
             tc_fence_after();
