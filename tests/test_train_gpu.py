@@ -212,3 +212,37 @@ def test_hash_single_step_other_table_sizes(pkg, orc, synth, log2):
     assert abs(int((gg != 0).sum()) - int((gr != 0).sum())) <= 2e-3 * int((gr != 0).sum()) + 4
     tr.close()
     net.destroy()
+
+
+@pytest.mark.parametrize("enc", [0, 1], ids=["frequency", "hash"])
+def test_fused_optimizer_is_bit_identical_to_the_standalone_optimizer_kernel(pkg, orc, synth, enc):
+    """The optimizer phase INSIDE the step kernel (matrix slice with prefetched state; Hash grid pass with the per-step learning-rate
+    table in shared memory and the branch-free update) against the stand-alone Adam + EMA kernel of the NCCL data-parallel path
+    (two powf per parameter), fed with the very same fp32 gradients: master weights, both Adam moments, training and EMA weights
+    must stay bit-identical over several steps on different batches -- from the second step on, hash-grid entries a batch missed
+    carry a lagging step count, which is exactly the case the table exists for.  (The 2-GPU test of the same property cannot run
+    on a 1-GPU box.)"""
+    import torch
+    a, tr = _make(pkg, orc, enc, seed=5)
+    b, tr_b = _make(pkg, orc, enc, seed=5)
+    tr.close(); tr_b.close()
+    kinds = (pkg.PARAMS_MASTER_F32, pkg.ADAM_M1_F32, pkg.ADAM_M2_F32, pkg.PARAMS_TRAIN_F16, pkg.PARAMS_EMA_F16, pkg.PARAMS_GRAD_F16)
+    nm = a.n_params()[1]
+    lagging = 0
+    for step in range(6):
+        q, t = _batch(synth, 300 + step % 4)          # four different batches in turn
+        qd, td = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+        a.train(qd, td)                               # fused: forward .. Adam + EMA in one launch
+        g = a.get_params(pkg.GRAD_F32)                # the fp32 gradient that launch reduced and applied
+        b.train_grad(qd, td, B, B)                    # (makes a gradient pending; its own values are replaced below)
+        b.set_params(pkg.GRAD_F32, g)
+        b.train_apply()                               # stand-alone optimizer kernel on the same gradient
+        for kind in kinds:
+            pa, pb = a.get_params(kind), b.get_params(kind)
+            assert np.array_equal(pa.view(np.uint8), pb.view(np.uint8)), \
+                f"step {step + 1}, kind {kind}: {np.mean(pa != pb):.2e} of the entries differ"
+        if enc == 1:
+            lagging = max(lagging, int(np.count_nonzero(g[nm:] == 0.0)))
+    if enc == 1:
+        assert lagging > 1000, "the batches were meant to miss some grid entries (lagging step counts)"
+    a.destroy(); b.destroy()
