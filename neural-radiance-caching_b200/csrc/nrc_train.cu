@@ -413,8 +413,11 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const bool has_tile = tile < n_data;
     const bool in_aligned = (reinterpret_cast<uintptr_t>(a.in) & 15) == 0 && a.perm_n == 0;   // bulk copy needs a contiguous tile
     uint32_t s = 0;                 // optimizer step within this launch
-    auto stamp = [&](int slot) { if (a.timeline && tid == 0 && s == 0) a.timeline[tile * 8 + slot] = clock64(); };
-    stamp(0);
+    // debug stamps: a single-step launch records its only step (slot 0 = kernel start), a multi-step launch its SECOND step
+    // (slot 0 = top of that step, i.e. right after step 0's optimizer phase: the in-launch steady state)
+    const uint32_t stamp_step = (MULTI && a.n_steps > 1) ? 1u : 0u;
+    auto stamp = [&](int slot) { if (a.timeline && tid == 0 && s == stamp_step) a.timeline[tile * 8 + slot] = clock64(); };
+    if (stamp_step == 0) stamp(0);
 
     if (tid == 0) {
         mbar_init(a_ready, kWorkerWarps); mbar_init(d_ready, 1); mbar_init(in_full, 1); mbar_init(w_full, 1); mbar_init(st_full, 1);
@@ -431,6 +434,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
     const uint32_t n_steps = MULTI ? a.n_steps : 1;
 
   for (s = 0; s < n_steps; ++s) {
+    if (stamp_step != 0) stamp(0);
     const uint32_t first = s * a.n_local + tile * kTT;   // first sample of this tile in this step
     // Frequency, s > 0: the CTA has only ARRIVED at the previous step's second grid barrier; the raw queries and their
     // encoding do not depend on the other CTAs, so they run while that barrier is pending, and the issuer warp completes
@@ -926,7 +930,7 @@ nrc_train_step_kernel(const TrainArgs a, const GridMeta gm) {
             level(std::integral_constant<int, 14>{}); level(std::integral_constant<int, 15>{});
         }
 #endif
-        if (a.timeline && tid == 128 && s == 0) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
+        if (a.timeline && tid == 128 && s == stamp_step) a.timeline[tile * 8 + 7] = clock64();   // half 1 done scattering (debug)
         {   // the last two accumulators: dW_in and dW_h1, all loads in flight before the wait
             constexpr int kInChunks = E / 16;                 // 5 (Frequency) / 4 (Hash)
             constexpr int kSplit = (kInChunks + 1) / 2;       // half 0: chunks [0, kSplit); half 1: the rest

@@ -23,6 +23,13 @@ for enc in (0, 1):
     print("enc", enc, " ".join(f"{n}={np.median(d[:, i]):.2f}us(max {d[:, i].max():.2f})" for i, n in enumerate(names)),
           f"total={np.median(tl[:, 6] - tl[:, 0]) / 1.965e3:.2f}us",
           f"half1-scatter-done at +{np.median(tl[:, 7] - tl[:, 3]) / 1.965e3:.2f}us after backward")
+    # the frame's four steps in ONE launch: the stamps are those of the launch's second step (slot 0 = top of that step)
+    for _ in range(3): net.train_batches(qa.data_ptr(), ta.data_ptr(), 4)
+    tl = net.debug_train_timeline(True, read=True).astype(np.float64)
+    d = np.diff(tl[:, :7], axis=1) / 1.965e3
+    names_m = ["(barrier 2 +) weights + encode", "forward", "backward+wgrad", "scatter+dump", "grid barrier", "reduce+adam"]
+    print("enc", enc, "4-step launch, step 2:", " ".join(f"{n}={np.median(d[:, i]):.2f}us(max {d[:, i].max():.2f})" for i, n in enumerate(names_m)),
+          f"total={np.median(tl[:, 6] - tl[:, 0]) / 1.965e3:.2f}us")
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     net.debug_train_timeline(False)
     torch.cuda.synchronize(); e0.record()
